@@ -1,0 +1,111 @@
+/* C ABI of librtdc_b200.so — the hand-written sm_100a kernels and native runtime pieces of
+ * ray_torch_distributed_checkpoint_b200. Python binds these with ctypes (ops/_lib.py); any other
+ * host language can do the same. Every function returns 0 on success, non-zero on failure, in which
+ * case rtdc_last_error() holds a message for the calling thread. All kernels are enqueued on the
+ * stream passed in (a cudaStream_t / CUstream as void*); nothing synchronises the device unless
+ * its comment says so.
+ *
+ * "ref:" comments cite the reference (outerbounds/ray-torch-distributed-checkpoint) line whose
+ * behaviour the entry point covers; the reference itself ships no native code.
+ */
+#ifndef RTDC_B200_H
+#define RTDC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* rtdc_last_error(void);
+/* Library/ABI version and the architecture the kernels were compiled for ("sm_100a"). */
+int rtdc_version(void);
+const char* rtdc_arch(void);
+
+/* ------------------------------------------------------------------------------------------
+ * GEMM on the 5th-generation tensor cores (tcgen05.mma kind::tf32, accumulators in TMEM, operands
+ * staged by TMA with 128-byte swizzle), fp32 in / fp32 out.
+ *   D[M,N] = epilogue( sum_k A(m,k) * B(n,k) )
+ * precision = 3: "3xTF32" — each fp32 operand tile is split in shared memory into a tf32 head and
+ *   a tf32 tail and three MMAs (tail*head + head*tail + head*head) accumulate in fp32, which
+ *   recovers fp32-GEMM accuracy (~2^-22 relative per product) on the tensor cores.
+ * precision = 1: single tf32 MMA (10-bit mantissa operands).
+ * Covers ref: my_ray_module.py:99-106 (Linear+ReLU+Dropout forward, K1-K3), :159 (backward
+ * dgrad/wgrad, K6), :279-282 (inference forward, K12).
+ */
+typedef struct rtdc_gemm_desc {
+  /* operands */
+  const float* a; int lda; int a_mn; /* a_mn=0: A is [M,K] row-major (K-major); 1: A is [K,M] row-major */
+  const float* b; int ldb; int b_mn; /* b_mn=0: B is [N,K] row-major (K-major); 1: B is [K,N] row-major */
+  int M, N, K;
+  /* output: out[m*ldo + n]; columns N..n_store-1 are written as 0 (padding kept clean) */
+  float* out; int ldo; int n_store;
+  /* epilogue, applied in this order */
+  const float* bias;      /* [N] added per column, or NULL */
+  int relu;               /* max(x,0) */
+  float drop_p;           /* inverted dropout with probability p (0 disables) */
+  uint64_t seed;          /* Philox key */
+  const uint32_t* step_ptr; /* device pointer to a step counter mixed into the Philox counter, or NULL */
+  uint32_t step_imm;      /* used when step_ptr is NULL */
+  uint32_t salt;          /* distinguishes layers sharing a seed */
+  const float* mask_src; int ldm; float mask_scale; /* x *= (mask_src[m*ldm+n] > 0) ? mask_scale : 0, or NULL */
+  /* execution */
+  int precision;          /* 3 or 1 */
+  int bn;                 /* N tile (0 = choose) */
+  int splits;             /* split-K factor (0 = choose). >1 needs scratch */
+  float* scratch; size_t scratch_bytes; /* split-K partial tiles + tile counters, see rtdc_gemm_scratch_bytes */
+} rtdc_gemm_desc;
+
+/* Bytes of scratch rtdc_gemm needs for this descriptor (0 when it will not split K). The first
+ * rtdc_gemm call on a scratch buffer expects its trailing counter words to be zero; calls leave
+ * them zero again. */
+size_t rtdc_gemm_scratch_bytes(const rtdc_gemm_desc* d);
+int rtdc_gemm(const rtdc_gemm_desc* d, void* stream);
+/* Tile/split plan the launcher would use: out[0]=bn, out[1]=stages, out[2]=splits, out[3]=grid.x, out[4]=smem bytes */
+int rtdc_gemm_plan(const rtdc_gemm_desc* d, int* out5);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused softmax-cross-entropy (K4/K5). logits [rows, ldz] (first `classes` columns valid),
+ * labels int64 [rows]. Writes the mean loss (sum/rows, ref: nn.CrossEntropyLoss() default,
+ * my_ray_module.py:141,156), optionally dlogits [rows, ldz] = (softmax - onehot) * grad_scale,
+ * multiplied by (logit > 0) when relu_mask != 0 (the reference's trailing ReLU, :106), padding
+ * columns zeroed; optionally counts argmax==label into correct (ref: :170).
+ * scratch: rtdc_softmax_ce_scratch_bytes(rows) bytes, zero before first use, left zero after.
+ */
+size_t rtdc_softmax_ce_scratch_bytes(int rows);
+int rtdc_softmax_ce(const float* logits, int ldz, const int64_t* labels, int rows, int classes,
+                    float* loss_out, float* dlogits, float grad_scale, int relu_mask,
+                    unsigned long long* correct_accum, float* loss_sum_accum,
+                    void* scratch, size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Column sums of a [rows, cols] fp32 matrix (bias gradients, K6): out[c] = sum_r x[r*ld + c].
+ * Deterministic two-stage reduction; scratch: rtdc_colsum_scratch_bytes(rows, cols).
+ */
+size_t rtdc_colsum_scratch_bytes(int rows, int cols);
+int rtdc_colsum(const float* x, int ld, int rows, int cols, float* out, void* scratch, size_t scratch_bytes,
+                void* stream);
+
+/* uint8 pixels -> normalised fp32 ((x/255 - mean)/std; ref: my_ray_module.py:38 ToTensor+Normalize). */
+int rtdc_u8_normalize(const uint8_t* src, float* dst, size_t n, float mean, float std, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused optimizer steps over a flat parameter arena (K7). hyper points to device memory so a
+ * captured CUDA graph sees updated values.
+ * SGD (ref: torch.optim.SGD(lr, momentum=0.9), my_ray_module.py:142,160):
+ *   g' = g*grad_scale + wd*p ; m = mu*m + (1-damp)*g' (m = g' on the first step) ; p -= lr*(nesterov ? g'+mu*m : m)
+ */
+typedef struct rtdc_sgd_hyper { float lr, momentum, dampening, weight_decay, grad_scale; int nesterov; int first_step; int pad; } rtdc_sgd_hyper;
+int rtdc_sgd_step(float* p, const float* g, float* m, size_t n, const rtdc_sgd_hyper* hyper_dev, void* stream);
+/* Adam / AdamW (decoupled != 0): step counter lives in hyper_dev->step and is advanced by rtdc_adam_advance. */
+typedef struct rtdc_adam_hyper { float lr, beta1, beta2, eps, weight_decay, grad_scale; int decoupled; int step; } rtdc_adam_hyper;
+int rtdc_adam_step(float* p, const float* g, float* m, float* v, size_t n, const rtdc_adam_hyper* hyper_dev, void* stream);
+int rtdc_adam_advance(rtdc_adam_hyper* hyper_dev, void* stream);
+/* step_counter[0] += 1 on the stream (dropout step counter, first_step flag clearing). */
+int rtdc_counter_advance(uint32_t* counter_dev, rtdc_sgd_hyper* sgd_hyper_or_null, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTDC_B200_H */

@@ -1,0 +1,410 @@
+// Memory-bound sm_100a kernels around the GEMMs: fused softmax-cross-entropy forward+backward
+// (K4/K5), deterministic column sums for bias gradients (K6), uint8->fp32 input normalisation
+// (K9 fused with the reference's ToTensor+Normalize), fused multi-tensor SGD / Adam over a flat
+// arena (K7). All are 128-bit vectorised grid-stride kernels sized to 148 SMs x resident CTAs.
+#include "common.h"
+#include "ptx.cuh"
+#include "../../include/rtdc_b200.h"
+
+namespace rtdc {
+
+constexpr int CE_THREADS = 256;
+constexpr int CE_MAX_BLOCKS = 1184;  // 148 SMs x 8 resident CTAs
+
+// ---------------------------------------------------------------------------------------------
+// softmax cross-entropy. One thread per row (classes <= 32 keeps a row in registers); block
+// partial sums go to scratch and the last block to finish adds them in block order, so the loss
+// is bit-reproducible. scratch layout: float partial[CE_MAX_BLOCKS]; u64 correct[CE_MAX_BLOCKS];
+// u32 counter.
+struct CeScratch {
+  unsigned int counter;
+  unsigned int pad[63];
+  float partial[CE_MAX_BLOCKS];
+  unsigned long long correct[CE_MAX_BLOCKS];
+};
+
+template <int MAXC>
+__global__ void __launch_bounds__(CE_THREADS)
+softmax_ce_kernel(const float* __restrict__ logits, int ldz, const long long* __restrict__ labels, int rows,
+                  int classes, float* __restrict__ loss_out, float* __restrict__ dlogits, float grad_scale,
+                  int relu_mask, unsigned long long* correct_accum, float* loss_sum_accum, CeScratch* scratch) {
+  __shared__ float s_loss[CE_THREADS / 32];
+  __shared__ unsigned int s_correct[CE_THREADS / 32];
+  __shared__ unsigned int s_last;
+  float my_loss = 0.f;
+  unsigned int my_correct = 0;
+  for (int row = blockIdx.x * blockDim.x + threadIdx.x; row < rows; row += gridDim.x * blockDim.x) {
+    const float* z = logits + static_cast<size_t>(row) * ldz;
+    float v[MAXC];
+    float mx = -INFINITY;
+    int arg = 0;
+    if ((ldz & 3) == 0) {
+#pragma unroll
+      for (int q = 0; q < MAXC / 4; ++q) {
+        if (q * 4 < ldz) {
+          const float4 t = __ldg(reinterpret_cast<const float4*>(z) + q);
+          v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < MAXC; ++j)
+        if (j < classes) v[j] = __ldg(z + j);
+    }
+#pragma unroll
+    for (int j = 0; j < MAXC; ++j) {
+      if (j < classes && v[j] > mx) { mx = v[j]; arg = j; }  // first maximum, like torch.argmax
+    }
+    float sum = 0.f;
+    float e[MAXC];
+#pragma unroll
+    for (int j = 0; j < MAXC; ++j) {
+      e[j] = (j < classes) ? __expf(v[j] - mx) : 0.f;
+      sum += e[j];
+    }
+    const long long y = labels[row];
+    float zy = 0.f;
+#pragma unroll
+    for (int j = 0; j < MAXC; ++j)
+      if (j == y) zy = v[j];
+    my_loss += (mx + __logf(sum)) - zy;
+    my_correct += (arg == y) ? 1u : 0u;
+    if (dlogits != nullptr) {
+      const float inv = grad_scale / sum;
+      float* dz = dlogits + static_cast<size_t>(row) * ldz;
+      float g[MAXC];
+#pragma unroll
+      for (int j = 0; j < MAXC; ++j) {
+        float t = 0.f;
+        if (j < classes) {
+          t = e[j] * inv - ((j == y) ? grad_scale : 0.f);
+          if (relu_mask && !(v[j] > 0.f)) t = 0.f;
+        }
+        g[j] = t;
+      }
+      if ((ldz & 3) == 0) {
+#pragma unroll
+        for (int q = 0; q < MAXC / 4; ++q)
+          if (q * 4 < ldz) reinterpret_cast<float4*>(dz)[q] = make_float4(g[4 * q], g[4 * q + 1], g[4 * q + 2], g[4 * q + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < MAXC; ++j)
+          if (j < ldz) dz[j] = g[j];
+      }
+    }
+  }
+  // block reduction
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    my_loss += __shfl_xor_sync(0xffffffffu, my_loss, o);
+    my_correct += __shfl_xor_sync(0xffffffffu, my_correct, o);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) { s_loss[warp] = my_loss; s_correct[warp] = my_correct; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float bl = 0.f;
+    unsigned int bc = 0;
+    for (int w = 0; w < CE_THREADS / 32; ++w) { bl += s_loss[w]; bc += s_correct[w]; }
+    scratch->partial[blockIdx.x] = bl;
+    scratch->correct[blockIdx.x] = bc;
+    __threadfence();
+    const unsigned int old = atomicAdd(&scratch->counter, 1u);
+    s_last = (old == gridDim.x - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    __threadfence();
+    float total = 0.f;
+    unsigned long long corr = 0;
+    for (unsigned int b = 0; b < gridDim.x; ++b) {
+      total += __ldcg(&scratch->partial[b]);
+      corr += __ldcg(&scratch->correct[b]);
+    }
+    if (loss_out) *loss_out = total / static_cast<float>(rows);
+    if (loss_sum_accum) *loss_sum_accum += total / static_cast<float>(rows);  // per-batch mean, summed (ref :168)
+    if (correct_accum) *correct_accum += corr;
+    scratch->counter = 0u;  // ready for the next launch
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// column sums: stage 1 = each block sums a row slab for 128 columns into partial[slab][col];
+// last block per column group sums the slabs in order.
+constexpr int CS_THREADS = 256;
+constexpr int CS_COLS = 128;     // columns per block: 32 lanes x float4
+constexpr int CS_MAX_SLABS = 64;
+
+__global__ void __launch_bounds__(CS_THREADS)
+colsum_kernel(const float* __restrict__ x, int ld, int rows, int cols, float* __restrict__ out, float* partial,
+              unsigned int* counters, int rows_per_slab) {
+  __shared__ float4 s_acc[CS_THREADS / 32][32];
+  __shared__ unsigned int s_last;
+  const int cg = blockIdx.x, slab = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c0 = cg * CS_COLS + lane * 4;
+  const int r_begin = slab * rows_per_slab, r_end = min(rows, r_begin + rows_per_slab);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  const bool vec = ((ld & 3) == 0) && (c0 + 3 < cols) && ((reinterpret_cast<uintptr_t>(x) & 15u) == 0);
+  for (int r = r_begin + warp; r < r_end; r += CS_THREADS / 32) {
+    const float* src = x + static_cast<size_t>(r) * ld + c0;
+    if (vec) {
+      const float4 t = __ldg(reinterpret_cast<const float4*>(src));
+      acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+    } else {
+      if (c0 < cols) acc.x += __ldg(src);
+      if (c0 + 1 < cols) acc.y += __ldg(src + 1);
+      if (c0 + 2 < cols) acc.z += __ldg(src + 2);
+      if (c0 + 3 < cols) acc.w += __ldg(src + 3);
+    }
+  }
+  s_acc[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0) {
+    float4 t = s_acc[0][lane];
+    for (int w = 1; w < CS_THREADS / 32; ++w) {
+      const float4 u = s_acc[w][lane];
+      t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+    }
+    float* dst = partial + (static_cast<size_t>(slab) * gridDim.x + cg) * CS_COLS + lane * 4;
+    *reinterpret_cast<float4*>(dst) = t;
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) {
+      const unsigned int old = atomicAdd(&counters[cg], 1u);
+      s_last = (old == gridDim.y - 1) ? 1u : 0u;
+      if (s_last) counters[cg] = 0u;
+    }
+    __syncwarp();
+    if (s_last) {
+      __threadfence();
+      float4 tot = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (unsigned int s = 0; s < gridDim.y; ++s) {
+        const float4 u = __ldcg(reinterpret_cast<const float4*>(partial + (static_cast<size_t>(s) * gridDim.x + cg) * CS_COLS + lane * 4));
+        tot.x += u.x; tot.y += u.y; tot.z += u.z; tot.w += u.w;
+      }
+      if (c0 < cols) out[c0] = tot.x;
+      if (c0 + 1 < cols) out[c0 + 1] = tot.y;
+      if (c0 + 2 < cols) out[c0 + 2] = tot.z;
+      if (c0 + 3 < cols) out[c0 + 3] = tot.w;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+u8_normalize_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst, size_t n, float scale, float shift) {
+  // 16 pixels per thread per iteration: one 128-bit load, four 128-bit stores
+  const size_t nvec = n / 16;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    const uint4 w = __ldg(reinterpret_cast<const uint4*>(src) + i);
+    const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+    float4* o = reinterpret_cast<float4*>(dst) + i * 4;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float4 f;
+      f.x = static_cast<float>(ws[q] & 0xFFu) * scale + shift;
+      f.y = static_cast<float>((ws[q] >> 8) & 0xFFu) * scale + shift;
+      f.z = static_cast<float>((ws[q] >> 16) & 0xFFu) * scale + shift;
+      f.w = static_cast<float>(ws[q] >> 24) * scale + shift;
+      o[q] = f;
+    }
+  }
+  if (blockIdx.x == 0) {
+    for (size_t i = nvec * 16 + threadIdx.x; i < n; i += blockDim.x) dst[i] = static_cast<float>(src[i]) * scale + shift;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, size_t n,
+           const rtdc_sgd_hyper* __restrict__ hp) {
+  const rtdc_sgd_hyper h = *hp;
+  const size_t nvec = n / 4;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const bool use_m = h.momentum != 0.f;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    float4 pv = reinterpret_cast<float4*>(p)[i];
+    const float4 gv = __ldg(reinterpret_cast<const float4*>(g) + i);
+    float4 mv = use_m ? reinterpret_cast<float4*>(m)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    float* pp = &pv.x; const float* gg = &gv.x; float* mm = &mv.x;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float gr = gg[j] * h.grad_scale + h.weight_decay * pp[j];
+      if (use_m) {
+        mm[j] = h.first_step ? gr : h.momentum * mm[j] + (1.f - h.dampening) * gr;
+        gr = h.nesterov ? gr + h.momentum * mm[j] : mm[j];
+      }
+      pp[j] -= h.lr * gr;
+    }
+    reinterpret_cast<float4*>(p)[i] = pv;
+    if (use_m) reinterpret_cast<float4*>(m)[i] = mv;
+  }
+  if (blockIdx.x == 0) {
+    for (size_t i = nvec * 4 + threadIdx.x; i < n; i += blockDim.x) {
+      float gr = g[i] * h.grad_scale + h.weight_decay * p[i];
+      if (use_m) {
+        const float mi = h.first_step ? gr : h.momentum * m[i] + (1.f - h.dampening) * gr;
+        m[i] = mi;
+        gr = h.nesterov ? gr + h.momentum * mi : mi;
+      }
+      p[i] -= h.lr * gr;
+    }
+  }
+}
+
+__device__ __forceinline__ void adam_update(float& p, float g, float& m, float& v, const rtdc_adam_hyper& h, float bc1,
+                                            float bc2_sqrt) {
+  g *= h.grad_scale;
+  if (h.decoupled) p *= (1.f - h.lr * h.weight_decay);
+  else g += h.weight_decay * p;
+  m = h.beta1 * m + (1.f - h.beta1) * g;
+  v = h.beta2 * v + (1.f - h.beta2) * g * g;
+  const float denom = sqrtf(v) / bc2_sqrt + h.eps;
+  p -= (h.lr / bc1) * (m / denom);
+}
+
+__global__ void __launch_bounds__(256)
+adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, size_t n,
+            const rtdc_adam_hyper* __restrict__ hp) {
+  const rtdc_adam_hyper h = *hp;
+  const float t = static_cast<float>(h.step);
+  const float bc1 = 1.f - powf(h.beta1, t);
+  const float bc2_sqrt = sqrtf(1.f - powf(h.beta2, t));
+  const size_t nvec = n / 4;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    float4 pv = reinterpret_cast<float4*>(p)[i];
+    const float4 gv = __ldg(reinterpret_cast<const float4*>(g) + i);
+    float4 mv = reinterpret_cast<float4*>(m)[i];
+    float4 vv = reinterpret_cast<float4*>(v)[i];
+    adam_update(pv.x, gv.x, mv.x, vv.x, h, bc1, bc2_sqrt);
+    adam_update(pv.y, gv.y, mv.y, vv.y, h, bc1, bc2_sqrt);
+    adam_update(pv.z, gv.z, mv.z, vv.z, h, bc1, bc2_sqrt);
+    adam_update(pv.w, gv.w, mv.w, vv.w, h, bc1, bc2_sqrt);
+    reinterpret_cast<float4*>(p)[i] = pv;
+    reinterpret_cast<float4*>(m)[i] = mv;
+    reinterpret_cast<float4*>(v)[i] = vv;
+  }
+  if (blockIdx.x == 0) {
+    for (size_t i = nvec * 4 + threadIdx.x; i < n; i += blockDim.x) adam_update(p[i], g[i], m[i], v[i], h, bc1, bc2_sqrt);
+  }
+}
+
+__global__ void adam_advance_kernel(rtdc_adam_hyper* h) { h->step += 1; }
+__global__ void counter_advance_kernel(uint32_t* c, rtdc_sgd_hyper* h) {
+  if (c) c[0] += 1u;
+  if (h) h->first_step = 0;
+}
+
+static int grid_for(size_t work_items, int threads, int per_sm) {
+  size_t blocks = (work_items + threads - 1) / threads;
+  const size_t cap = static_cast<size_t>(148) * per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+}  // namespace rtdc
+
+using namespace rtdc;
+
+RTDC_API const char* rtdc_last_error(void) { return error_buffer(); }
+RTDC_API int rtdc_version(void) { return 1; }
+RTDC_API const char* rtdc_arch(void) { return "sm_100a"; }
+
+RTDC_API size_t rtdc_softmax_ce_scratch_bytes(int) { return sizeof(CeScratch); }
+
+RTDC_API int rtdc_softmax_ce(const float* logits, int ldz, const int64_t* labels, int rows, int classes,
+                             float* loss_out, float* dlogits, float grad_scale, int relu_mask,
+                             unsigned long long* correct_accum, float* loss_sum_accum, void* scratch,
+                             size_t scratch_bytes, void* stream) {
+  if (!logits || !labels || rows <= 0) return fail(RTDC_ERR_ARG, "logits/labels null or rows <= 0");
+  if (classes < 1 || classes > 32 || ldz < classes) return fail(RTDC_ERR_LIMIT, "softmax_ce supports 1..32 classes with ldz >= classes (got %d, ldz %d)", classes, ldz);
+  if ((ldz & 3) == 0 && ldz > 32) return fail(RTDC_ERR_LIMIT, "softmax_ce: ldz must be <= 32 (got %d)", ldz);
+  if (!scratch || scratch_bytes < sizeof(CeScratch)) return fail(RTDC_ERR_ARG, "softmax_ce needs %zu bytes of scratch", sizeof(CeScratch));
+  const int blocks = grid_for(static_cast<size_t>(rows), CE_THREADS, 8);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (classes <= 16 && ldz <= 16)
+    softmax_ce_kernel<16><<<blocks, CE_THREADS, 0, st>>>(logits, ldz, reinterpret_cast<const long long*>(labels), rows, classes, loss_out, dlogits, grad_scale, relu_mask, correct_accum, loss_sum_accum, static_cast<CeScratch*>(scratch));
+  else
+    softmax_ce_kernel<32><<<blocks, CE_THREADS, 0, st>>>(logits, ldz, reinterpret_cast<const long long*>(labels), rows, classes, loss_out, dlogits, grad_scale, relu_mask, correct_accum, loss_sum_accum, static_cast<CeScratch*>(scratch));
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
+static void colsum_shape(int rows, int cols, int* col_groups, int* slabs, int* rows_per_slab) {
+  *col_groups = ceil_div(cols, CS_COLS);
+  int s = (148 * 4) / *col_groups;
+  if (s > CS_MAX_SLABS) s = CS_MAX_SLABS;
+  const int max_by_rows = ceil_div(rows, 64);
+  if (s > max_by_rows) s = max_by_rows;
+  if (s < 1) s = 1;
+  *rows_per_slab = ceil_div(rows, s);
+  *slabs = ceil_div(rows, *rows_per_slab);
+}
+
+constexpr size_t CS_COUNTER_BYTES = 4096;  // counters first, at a fixed place (see gemm_tf32.cu)
+RTDC_API size_t rtdc_colsum_scratch_bytes(int rows, int cols) {
+  int cg, slabs, rps;
+  colsum_shape(rows, cols, &cg, &slabs, &rps);
+  return CS_COUNTER_BYTES + static_cast<size_t>(slabs) * cg * CS_COLS * 4;
+}
+
+RTDC_API int rtdc_colsum(const float* x, int ld, int rows, int cols, float* out, void* scratch, size_t scratch_bytes,
+                         void* stream) {
+  if (!x || !out || rows <= 0 || cols <= 0 || ld < cols) return fail(RTDC_ERR_ARG, "colsum: bad arguments");
+  int cg, slabs, rps;
+  colsum_shape(rows, cols, &cg, &slabs, &rps);
+  const size_t need = rtdc_colsum_scratch_bytes(rows, cols);
+  if (!scratch || scratch_bytes < need) return fail(RTDC_ERR_ARG, "colsum needs %zu bytes of scratch (got %zu)", need, scratch_bytes);
+  if (static_cast<size_t>(cg) * 4 > CS_COUNTER_BYTES) return fail(RTDC_ERR_LIMIT, "colsum supports at most %zu columns", CS_COUNTER_BYTES / 4 * CS_COLS);
+  unsigned int* counters = static_cast<unsigned int*>(scratch);
+  float* partial = reinterpret_cast<float*>(static_cast<uint8_t*>(scratch) + CS_COUNTER_BYTES);
+  colsum_kernel<<<dim3(cg, slabs), CS_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x, ld, rows, cols, out, partial, counters, rps);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
+RTDC_API int rtdc_u8_normalize(const uint8_t* src, float* dst, size_t n, float mean, float std, void* stream) {
+  if (!src || !dst) return fail(RTDC_ERR_ARG, "u8_normalize: null pointer");
+  if (n == 0) return RTDC_OK;
+  if ((reinterpret_cast<uintptr_t>(src) & 15u) || (reinterpret_cast<uintptr_t>(dst) & 15u)) return fail(RTDC_ERR_ARG, "u8_normalize: pointers must be 16-byte aligned");
+  const float scale = 1.0f / (255.0f * std), shift = -mean / std;
+  u8_normalize_kernel<<<grid_for(n / 16 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(src, dst, n, scale, shift);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
+RTDC_API int rtdc_sgd_step(float* p, const float* g, float* m, size_t n, const rtdc_sgd_hyper* hyper_dev, void* stream) {
+  if (!p || !g || !hyper_dev) return fail(RTDC_ERR_ARG, "sgd_step: null pointer");
+  if (n == 0) return RTDC_OK;
+  if ((reinterpret_cast<uintptr_t>(p) & 15u) || (reinterpret_cast<uintptr_t>(g) & 15u) || (reinterpret_cast<uintptr_t>(m) & 15u))
+    return fail(RTDC_ERR_ARG, "sgd_step: arenas must be 16-byte aligned");
+  sgd_kernel<<<grid_for(n / 4 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, n, hyper_dev);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
+RTDC_API int rtdc_adam_step(float* p, const float* g, float* m, float* v, size_t n, const rtdc_adam_hyper* hyper_dev, void* stream) {
+  if (!p || !g || !m || !v || !hyper_dev) return fail(RTDC_ERR_ARG, "adam_step: null pointer");
+  if (n == 0) return RTDC_OK;
+  if ((reinterpret_cast<uintptr_t>(p) & 15u) || (reinterpret_cast<uintptr_t>(g) & 15u) || (reinterpret_cast<uintptr_t>(m) & 15u) || (reinterpret_cast<uintptr_t>(v) & 15u))
+    return fail(RTDC_ERR_ARG, "adam_step: arenas must be 16-byte aligned");
+  adam_kernel<<<grid_for(n / 4 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, v, n, hyper_dev);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
+RTDC_API int rtdc_adam_advance(rtdc_adam_hyper* hyper_dev, void* stream) {
+  adam_advance_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(hyper_dev);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
+RTDC_API int rtdc_counter_advance(uint32_t* counter_dev, rtdc_sgd_hyper* sgd_hyper_or_null, void* stream) {
+  counter_advance_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(counter_dev, sgd_hyper_or_null);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}

@@ -1,0 +1,83 @@
+"""Entry point of one worker process started by ``TorchTrainer.fit()`` (driver mode).
+
+Does what a Ray Train worker actor does before calling the user's function (implicit at
+``/root/reference/my_ray_module.py:244-250``): read the rendezvous environment, join the process
+group (``nccl`` when ``use_gpu`` else ``gloo``), install the session, run
+``train_loop_per_worker(config)``, report completion or the traceback to the driver.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import traceback
+
+
+def main(payload_path: str) -> int:
+    import cloudpickle  # noqa: F401  (registers reducers used by pickle.load below)
+    import pickle
+
+    with open(payload_path, "rb") as f:
+        head = f.read()
+    # make the driver's import roots visible before unpickling user code
+    # (sys_path is stored in the payload itself, so peek with a tolerant first pass)
+    try:
+        payload = pickle.loads(head)
+    except ModuleNotFoundError:
+        payload = None
+    if payload is None:
+        sys.path.insert(0, os.getcwd())
+        payload = pickle.loads(head)
+    for p in payload.get("sys_path", []):
+        if p not in sys.path:
+            sys.path.append(p)
+
+    from ..train.link import SocketLink
+    from ..train.session import TrainContext, _Session, _set_session
+    from ..train.trainer import _call_train_fn
+
+    rank = int(os.environ["RANK"])
+    world = int(os.environ["WORLD_SIZE"])
+    local_rank = int(os.environ.get("LOCAL_RANK", rank))
+    link = SocketLink(payload["socket"], payload["authkey"], rank)
+    try:
+        import torch
+        import torch.distributed as dist
+
+        use_gpu = payload["use_gpu"]
+        if use_gpu:
+            torch.cuda.set_device(local_rank)
+        if world > 1:
+            kwargs = {"device_id": torch.device("cuda", local_rank)} if use_gpu else {}
+            dist.init_process_group(backend=payload["backend"], rank=rank, world_size=world, **kwargs)
+        storage = payload["storage"]
+        ctx = TrainContext(rank, world, local_rank, int(os.environ.get("LOCAL_WORLD_SIZE", world)),
+                           int(os.environ.get("NODE_RANK", 0)), payload["experiment_name"], payload["trial_name"],
+                           storage.trial_path, storage, use_gpu, payload.get("metadata"))
+        _set_session(_Session(ctx, link, payload.get("start_checkpoint"), payload.get("start_index", 0)))
+        _call_train_fn(payload["fn"], payload["config"])
+        if use_gpu:
+            torch.cuda.synchronize()
+        from ..ckpt import async_writer
+        async_writer.wait_all()
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        link.done()
+        return 0
+    except SystemExit as e:
+        return int(e.code or 0)
+    except BaseException:
+        tb = traceback.format_exc()
+        sys.stderr.write(tb)
+        link.error(tb)
+        return 1
+    finally:
+        _set_session(None)
+        link.close()
+
+
+if __name__ == "__main__":
+    code = main(sys.argv[1])
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(code)

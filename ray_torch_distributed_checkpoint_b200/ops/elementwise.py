@@ -1,0 +1,132 @@
+"""Python face of ``csrc/elementwise.cu``: fused softmax-cross-entropy, column sums, uint8 input
+normalisation, fused SGD / Adam steps over flat arenas.
+
+Reference parity: ``nn.CrossEntropyLoss`` (``/root/reference/my_ray_module.py:141,156,159``),
+``torch.optim.SGD(lr, momentum=0.9)`` (``:142,160``), ``ToTensor()+Normalize((0.5,),(0.5,))`` (``:38``),
+validation accuracy count (``:170``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import AdamHyper, SgdHyper
+from .gemm import scratch_for
+
+
+def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor, *, classes: Optional[int] = None,
+                          dlogits: Optional[torch.Tensor] = None, grad_scale: Optional[float] = None,
+                          relu_mask: bool = False, loss_out: Optional[torch.Tensor] = None,
+                          correct_accum: Optional[torch.Tensor] = None, loss_sum_accum: Optional[torch.Tensor] = None,
+                          stream=None) -> torch.Tensor:
+    """Mean cross-entropy of ``logits[:, :classes]``; optionally also writes
+    ``dlogits = (softmax - onehot) * grad_scale`` (default ``1/rows``), masked by ``logits > 0`` when
+    ``relu_mask`` (the reference model ends in a ReLU), and accumulates the number of correct
+    argmax predictions into ``correct_accum`` (uint64/int64 scalar on the device)."""
+    if logits.dtype != torch.float32 or not logits.is_cuda or logits.dim() != 2 or logits.stride(1) != 1:
+        raise ValueError("logits must be a 2-D float32 CUDA tensor with unit inner stride")
+    if labels.dtype != torch.int64 or not labels.is_contiguous():
+        raise ValueError("labels must be a contiguous int64 tensor")
+    rows = logits.shape[0]
+    classes = logits.shape[1] if classes is None else classes
+    if loss_out is None:
+        loss_out = torch.empty((), dtype=torch.float32, device=logits.device)
+    if dlogits is not None and (dlogits.stride(0) != logits.stride(0) or dlogits.dtype != torch.float32):
+        raise ValueError("dlogits must match the logits layout")
+    lib = _lib.load()
+    ws = scratch_for("ce", lib.rtdc_softmax_ce_scratch_bytes(rows), logits.device, stream)
+    gs = (1.0 / rows) if grad_scale is None else grad_scale
+    _lib.check(lib.rtdc_softmax_ce(
+        logits.data_ptr(), logits.stride(0), labels.data_ptr(), rows, classes, loss_out.data_ptr(),
+        dlogits.data_ptr() if dlogits is not None else None, gs, int(relu_mask),
+        correct_accum.data_ptr() if correct_accum is not None else None,
+        loss_sum_accum.data_ptr() if loss_sum_accum is not None else None,
+        ws.data_ptr(), ws.numel(), _lib.stream_ptr(stream)))
+    return loss_out
+
+
+def colsum(x: torch.Tensor, *, cols: Optional[int] = None, out: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
+    """``out[c] = sum_r x[r, c]`` for the first ``cols`` columns (bias gradient)."""
+    if x.dtype != torch.float32 or not x.is_cuda or x.dim() != 2 or x.stride(1) != 1:
+        raise ValueError("x must be a 2-D float32 CUDA tensor with unit inner stride")
+    rows = x.shape[0]
+    cols = x.shape[1] if cols is None else cols
+    if out is None:
+        out = torch.empty(cols, dtype=torch.float32, device=x.device)
+    lib = _lib.load()
+    ws = scratch_for("colsum", lib.rtdc_colsum_scratch_bytes(rows, cols), x.device, stream)
+    _lib.check(lib.rtdc_colsum(x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), ws.data_ptr(), ws.numel(),
+                               _lib.stream_ptr(stream)))
+    return out
+
+
+def u8_normalize(src: torch.Tensor, *, mean: float = 0.5, std: float = 0.5, out: Optional[torch.Tensor] = None,
+                 stream=None) -> torch.Tensor:
+    """uint8 pixels -> float32 ``(x/255 - mean)/std``, any shape (contiguous)."""
+    if src.dtype != torch.uint8 or not src.is_cuda or not src.is_contiguous():
+        raise ValueError("src must be a contiguous uint8 CUDA tensor")
+    if out is None:
+        out = torch.empty(src.shape, dtype=torch.float32, device=src.device)
+    _lib.check(_lib.load().rtdc_u8_normalize(src.data_ptr(), out.data_ptr(), src.numel(), mean, std, _lib.stream_ptr(stream)))
+    return out
+
+
+def _hyper_tensor(struct, device) -> torch.Tensor:
+    raw = bytes(struct)
+    return torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(device)
+
+
+class SgdState:
+    """Device-resident SGD hyper-parameters (readable by captured CUDA graphs) + host mirror."""
+
+    def __init__(self, device, lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False, grad_scale=1.0):
+        self.host = SgdHyper(lr, momentum, dampening, weight_decay, grad_scale, int(nesterov), 1, 0)
+        self.dev = _hyper_tensor(self.host, device)
+
+    def update(self, **kw):
+        for k, v in kw.items():
+            setattr(self.host, k, v)
+        self.dev.copy_(torch.frombuffer(bytearray(bytes(self.host)), dtype=torch.uint8), non_blocking=False)
+
+
+def sgd_step(p: torch.Tensor, g: torch.Tensor, m: Optional[torch.Tensor], state: SgdState, stream=None):
+    """One fused SGD(+momentum) step over flat fp32 arenas (in place on ``p`` and ``m``)."""
+    n = p.numel()
+    if g.numel() != n or (m is not None and m.numel() != n):
+        raise ValueError("arena sizes differ")
+    _lib.check(_lib.load().rtdc_sgd_step(p.data_ptr(), g.data_ptr(), m.data_ptr() if m is not None else p.data_ptr(), n,
+                                         state.dev.data_ptr(), _lib.stream_ptr(stream)))
+
+
+def counter_advance(counter: Optional[torch.Tensor], sgd_state: Optional[SgdState] = None, stream=None):
+    """``counter += 1`` on the stream; also clears ``first_step`` of an SGD state."""
+    _lib.check(_lib.load().rtdc_counter_advance(counter.data_ptr() if counter is not None else None,
+                                                sgd_state.dev.data_ptr() if sgd_state is not None else None,
+                                                _lib.stream_ptr(stream)))
+    if sgd_state is not None:
+        sgd_state.host.first_step = 0
+
+
+class AdamState:
+    def __init__(self, device, lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, decoupled=False, grad_scale=1.0):
+        self.host = AdamHyper(lr, betas[0], betas[1], eps, weight_decay, grad_scale, int(decoupled), 0)
+        self.dev = _hyper_tensor(self.host, device)
+
+    def update(self, **kw):
+        # the step counter lives on the device; preserve it
+        cur = AdamHyper.from_buffer_copy(bytes(self.dev.cpu().numpy().tobytes()))
+        for k, v in kw.items():
+            setattr(cur, k, v)
+        self.host = cur
+        self.dev.copy_(torch.frombuffer(bytearray(bytes(cur)), dtype=torch.uint8))
+
+
+def adam_step(p, g, m, v, state: AdamState, stream=None):
+    """Advance the device step counter, then one fused Adam/AdamW step over flat fp32 arenas."""
+    lib = _lib.load()
+    sp = _lib.stream_ptr(stream)
+    _lib.check(lib.rtdc_adam_advance(state.dev.data_ptr(), sp))
+    _lib.check(lib.rtdc_adam_step(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), state.dev.data_ptr(), sp))

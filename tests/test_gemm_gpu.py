@@ -1,0 +1,127 @@
+"""tcgen05 GEMM (csrc/gemm_tf32.cu) against plain PyTorch references computed in fp64."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ops():
+    from ray_torch_distributed_checkpoint_b200 import ops
+    return ops
+
+
+def _rel_err(got, ref64, scale64):
+    return ((got.double() - ref64).abs() / scale64.clamp_min(1e-30)).max().item()
+
+
+@pytest.mark.parametrize("M,N,K", [(300, 512, 784), (128, 256, 64), (1000, 512, 512), (77, 48, 40)])
+@pytest.mark.parametrize("precision,tol", [(3, 4e-6), (1, 3e-3)])
+def test_forward_kmajor(M, N, K, precision, tol):
+    ops = _ops()
+    g = torch.Generator(device="cuda").manual_seed(1)
+    x = torch.randn(M, K, device="cuda", generator=g)
+    w = torch.randn(N, K, device="cuda", generator=g) * 0.05
+    b = torch.randn(N, device="cuda", generator=g)
+    y = ops.linear_forward(x, w, b, precision=precision)
+    ref = x.double() @ w.double().T + b.double()
+    scale = x.double().abs() @ w.double().abs().T + b.double().abs()
+    assert _rel_err(y, ref, scale) < tol
+    # fp32-equivalent mode must be at least as close to fp64 as torch's own fp32 GEMM, within 4x
+    if precision == 3:
+        torch_err = _rel_err(torch.addmm(b, x, w.T), ref, scale)
+        assert _rel_err(y, ref, scale) < max(4 * torch_err, 1e-6)
+
+
+def test_forward_relu_dropout_matches_philox():
+    ops = _ops()
+    from ray_torch_distributed_checkpoint_b200.ops.philox_ref import dropout_keep_mask
+    M, N, K, p = 260, 512, 784, 0.25
+    g = torch.Generator(device="cuda").manual_seed(2)
+    x = torch.randn(M, K, device="cuda", generator=g)
+    w = torch.randn(N, K, device="cuda", generator=g) * 0.05
+    b = torch.randn(N, device="cuda", generator=g)
+    step_t = torch.tensor([7], dtype=torch.int32, device="cuda")
+    y = ops.linear_forward(x, w, b, relu=True, drop_p=p, seed=0x1234567890ABCDEF, step_tensor=step_t, salt=3)
+    keep = torch.from_numpy(dropout_keep_mask(M, N, p, 0x1234567890ABCDEF, step=7, salt=3)).cuda()
+    ref = torch.relu(x.double() @ w.double().T + b.double()) * keep / (1 - p)
+    scale = (x.double().abs() @ w.double().abs().T + b.double().abs()) / (1 - p)
+    assert _rel_err(y, ref, scale) < 4e-6
+    assert (y[~keep] == 0).all()
+    frac = keep.float().mean().item()
+    assert abs(frac - 0.75) < 0.01
+    # a different step draws a different mask
+    y2 = ops.linear_forward(x, w, b, relu=True, drop_p=p, seed=0x1234567890ABCDEF, step=8, salt=3)
+    assert ((y2 == 0) != (y == 0)).any()
+
+
+def test_forward_skinny_n_padded_store():
+    ops = _ops()
+    M, N, K = 515, 10, 512
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.randn(M, K, device="cuda", generator=g)
+    w = torch.randn(N, K, device="cuda", generator=g) * 0.05
+    b = torch.randn(N, device="cuda", generator=g)
+    out = torch.full((M, 16), 9.0, device="cuda")
+    ops.linear_forward(x, w, b, relu=True, out=out, n_store=16)
+    ref = torch.relu(x.double() @ w.double().T + b.double())
+    scale = x.double().abs() @ w.double().abs().T + b.double().abs()
+    assert _rel_err(out[:, :10], ref, scale) < 4e-6
+    assert (out[:, 10:] == 0).all()
+
+
+@pytest.mark.parametrize("B,n_out,k_in,ld_dy", [(300, 512, 512, 512), (515, 10, 512, 16), (256, 512, 784, 512)])
+def test_dgrad_with_mask(B, n_out, k_in, ld_dy):
+    ops = _ops()
+    g = torch.Generator(device="cuda").manual_seed(4)
+    dy = torch.zeros(B, ld_dy, device="cuda")
+    dy[:, :n_out] = torch.randn(B, n_out, device="cuda", generator=g)
+    w = torch.randn(n_out, k_in, device="cuda", generator=g) * 0.05
+    h = torch.relu(torch.randn(B, k_in, device="cuda", generator=g))
+    dx = ops.linear_dgrad(dy, w, N_out=n_out, mask_src=h, mask_scale=1.0 / 0.75)
+    ref = (dy[:, :n_out].double() @ w.double()) * (h > 0) / 0.75
+    scale = (dy[:, :n_out].double().abs() @ w.double().abs()) / 0.75
+    assert _rel_err(dx, ref, scale) < 4e-6
+
+
+@pytest.mark.parametrize("B,n_out,k_in,ld_dy", [(4096, 512, 784, 512), (4096, 512, 512, 512), (2080, 10, 512, 16), (100, 64, 96, 64)])
+@pytest.mark.parametrize("splits", [0, 1])
+def test_wgrad(B, n_out, k_in, ld_dy, splits):
+    ops = _ops()
+    g = torch.Generator(device="cuda").manual_seed(5)
+    dy = torch.zeros(B, ld_dy, device="cuda")
+    dy[:, :n_out] = torch.randn(B, n_out, device="cuda", generator=g)
+    x = torch.randn(B, k_in, device="cuda", generator=g)
+    ref = dy[:, :n_out].double().T @ x.double()
+    scale = dy[:, :n_out].double().abs().T @ x.double().abs()
+    for _ in range(2):  # second call reuses the scratch and its self-resetting counters
+        dw = ops.linear_wgrad(dy, x, N_out=n_out, splits=splits)
+        assert dw.shape == (n_out, k_in)
+        # one fp32 accumulator over the whole batch when splits == 1: allow sqrt(K) growth
+        assert _rel_err(dw, ref, scale) < (4e-6 if splits == 0 else 1.2e-5)
+
+
+def test_wgrad_into_bucket_view():
+    ops = _ops()
+    B, n_out, k_in = 2048, 512, 784
+    g = torch.Generator(device="cuda").manual_seed(6)
+    dy = torch.randn(B, n_out, device="cuda", generator=g)
+    x = torch.randn(B, k_in, device="cuda", generator=g)
+    bucket = torch.zeros(512 + n_out * k_in + 128, device="cuda")
+    view = bucket[512:512 + n_out * k_in].view(n_out, k_in)
+    ops.linear_wgrad(dy, x, out=view)
+    ref = dy.double().T @ x.double()
+    assert _rel_err(view, ref, dy.double().abs().T @ x.double().abs()) < 4e-6
+    assert (bucket[:512] == 0).all() and (bucket[512 + n_out * k_in:] == 0).all()
+
+
+def test_plan_and_errors():
+    ops = _ops()
+    plan = ops.gemm_plan(16384, 512, 784)
+    assert plan["bn"] == 256 and plan["splits"] == 1
+    plan = ops.gemm_plan(512, 784, 16384, b_mn=True)
+    assert plan["bn"] % 32 == 0 and plan["splits"] > 1
+    x = torch.randn(64, 30, device="cuda")  # leading dimension not a multiple of 4 floats
+    w = torch.randn(32, 30, device="cuda")
+    with pytest.raises(ops.RtdcError):
+        ops.linear_forward(x, w)
