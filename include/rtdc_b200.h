@@ -54,12 +54,12 @@ typedef struct rtdc_gemm_desc {
   int precision;          /* 3 or 1 */
   int bn;                 /* N tile (0 = choose) */
   int splits;             /* split-K factor (0 = choose). >1 needs scratch */
-  float* scratch; size_t scratch_bytes; /* split-K partial tiles + tile counters, see rtdc_gemm_scratch_bytes */
+  float* scratch; size_t scratch_bytes; /* split-K partial tiles, see rtdc_gemm_scratch_bytes */
 } rtdc_gemm_desc;
 
-/* Bytes of scratch rtdc_gemm needs for this descriptor (0 when it will not split K). The first
- * rtdc_gemm call on a scratch buffer expects its trailing counter words to be zero; calls leave
- * them zero again. */
+/* Bytes of scratch rtdc_gemm needs for this descriptor (0 when it will not split K): room for the
+ * per-split partial tiles, which a second kernel sums in split order. Contents need no initialisation.
+ * Calls that share a scratch buffer must not overlap on the GPU. */
 size_t rtdc_gemm_scratch_bytes(const rtdc_gemm_desc* d);
 int rtdc_gemm(const rtdc_gemm_desc* d, void* stream);
 /* Tile/split plan the launcher would use: out[0]=bn, out[1]=stages, out[2]=splits, out[3]=grid.x, out[4]=smem bytes */
@@ -104,6 +104,49 @@ int rtdc_adam_step(float* p, const float* g, float* m, float* v, size_t n, const
 int rtdc_adam_advance(rtdc_adam_hyper* hyper_dev, void* stream);
 /* step_counter[0] += 1 on the stream (dropout step counter, first_step flag clearing). */
 int rtdc_counter_advance(uint32_t* counter_dev, rtdc_sgd_hyper* sgd_hyper_or_null, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Symmetric memory + collectives over NVLink 5 / NVSwitch (C1-C5). One process per GPU; each rank
+ * calls rtdc_symm_create with the same `bytes` and the same rendezvous prefix (a path prefix for
+ * unix sockets, e.g. "/tmp/rtdc_<job>"); the call exchanges POSIX fd handles of cuMemCreate
+ * allocations and maps every peer. Then, after any host-level barrier between the ranks, each calls
+ * rtdc_symm_bind_multicast (NVLS; silently stays off where unsupported).
+ * ref: replaces the NCCL process group that Ray Train / torch DDP set up implicitly
+ * (my_ray_module.py:135,244-250).
+ */
+#define RTDC_SYMM_MAX_WORLD 8
+#define RTDC_SYMM_MAX_BLOCKS 64
+typedef struct rtdc_symm_info_t {
+  int rank, world, device;
+  size_t bytes;               /* usable bytes per rank */
+  void* local_ptr;            /* this rank's buffer */
+  void* multicast_ptr;        /* NVLS address covering all ranks' buffers, or NULL */
+  void* peer_ptrs[RTDC_SYMM_MAX_WORLD]; /* every rank's buffer as mapped here */
+  void** peer_table_dev;      /* device array of the same pointers */
+  void** pad_table_dev;       /* device array of per-rank signal pads */
+  unsigned int* epochs_dev;   /* per-block barrier epochs (local) */
+} rtdc_symm_info_t;
+int rtdc_symm_create(int rank, int world, int device, size_t bytes, const char* rendezvous_prefix,
+                     int enable_multicast, double timeout_s, void** out_handle);
+int rtdc_symm_bind_multicast(void* handle);
+int rtdc_symm_info(void* handle, rtdc_symm_info_t* out);
+int rtdc_symm_destroy(void* handle);
+
+/* In-place all-reduce (sum, then * scale) of `count` elements at byte `offset` of every rank's
+ * symmetric buffer. Every rank must issue the same sequence of collective calls on a handle.
+ *   algo: 0 = choose by size, 1 = one-shot (out-of-place into `out_local`, which must not alias the
+ *         symmetric buffer), 2 = two-shot (reduce-scatter + all-gather over P2P loads/stores),
+ *         3 = NVLS (multimem.ld_reduce + multimem.st through the switch; needs multicast_ptr).
+ *   dtype: 0 = fp32, 1 = bf16 (accumulated in fp32).
+ * The sum is formed in rank order 0..world-1 by a single owner per element (algo 1: by everyone in
+ * the same order), so all ranks end with bit-identical values.
+ * ref: the DDP gradient bucket all-reduce with its 1/world pre-scale (C3; my_ray_module.py:159). */
+int rtdc_symm_all_reduce(void* handle, size_t offset, size_t count, int dtype, float scale, int algo,
+                         void* out_local, int max_blocks, void* stream);
+/* Copy `bytes` at `offset` of rank `root`'s symmetric buffer into dst_local on every rank (C2/C4). */
+int rtdc_symm_broadcast(void* handle, size_t offset, size_t bytes, int root, void* dst_local, void* stream);
+/* Device-side barrier across ranks on the stream (C5). */
+int rtdc_symm_barrier(void* handle, void* stream);
 
 #ifdef __cplusplus
 }

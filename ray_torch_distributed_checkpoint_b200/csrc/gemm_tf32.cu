@@ -16,6 +16,8 @@
 //   MN-major: row-major [K, rows]   -> rows/32 TMA boxes of [32 k][32 floats]
 // so forward (X.W^T), dgrad (dY.W) and wgrad (dY^T.X) all run on this kernel with no transposes
 // in memory (K1-K3, K6, K12 in SURVEY.md §2.5).
+#include <stdlib.h>
+
 #include "common.h"
 #include "ptx.cuh"
 #include "../../include/rtdc_b200.h"
@@ -23,7 +25,8 @@
 namespace rtdc {
 
 constexpr int BM = 128;           // tile rows == TMEM lanes
-constexpr int BK = 32;            // fp32 elements per K block == one 128-byte swizzle row
+// K block (fp32 elements per pipeline stage): 32 = one 128-byte swizzle row, 16 = one 64-byte row.
+// 3xTF32 uses 16 so that four stages (raw + tail tiles) fit in shared memory.
 constexpr int UMMA_K = 8;         // tf32: 32 bytes per instruction along K
 constexpr int MAX_STAGES = 4;
 constexpr int MAX_BN = 256;
@@ -31,6 +34,7 @@ constexpr int TMEM_COLS = 256;
 constexpr int NUM_THREADS = 192;  // 6 warps
 constexpr int EPI_THREADS = 128;  // warps 2..5
 constexpr int SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
+constexpr int STATIC_SMEM_RESERVE = 2048;  // barriers, bias slice, flags (static __shared__)
 
 struct GemmParams {
   int M, N, K;
@@ -41,7 +45,10 @@ struct GemmParams {
   const float* bias; int relu;
   float drop_scale; uint32_t drop_thr16; uint32_t seed_lo, seed_hi; const uint32_t* step_ptr; uint32_t step_imm, salt;
   const float* mask_src; int ldm; float mask_scale;
-  float* scratch; unsigned int* counters;
+  float* scratch;
+  int debug;  // timing experiments only (RTDC_GEMM_DEBUG): 1 = no TMA loads, 2 = no MMAs, 4 = no global stores
+  int tma_store;         // epilogue goes through smem + cp.async.bulk.tensor stores (tmOut valid)
+  long long* dbg_times;  // RTDC_GEMM_DEBUG_BUF: per-CTA clock64 stamps [grid][8]
 };
 
 // keep flag for dropout: 16 random bits per element, 8 elements per Philox call.
@@ -50,17 +57,17 @@ __device__ __forceinline__ uint32_t rand16(const Philox4& r, int j) {
   return (j & 1) ? (w >> 16) : (w & 0xFFFFu);
 }
 
-template <bool A_MN, bool B_MN, int NSPLIT>
+template <bool A_MN, bool B_MN, int NSPLIT, int BK>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const GemmParams p) {
+                 const __grid_constant__ CUtensorMap tmOut, const GemmParams p) {
   extern __shared__ uint8_t smem_dyn[];
   __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t ready_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t accum_bar;
   __shared__ uint32_t tmem_base_slot;
-  __shared__ uint32_t last_flag;
+  __shared__ float s_bias[MAX_BN];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -96,6 +103,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (p.tma_store) tma_prefetch_desc(&tmOut);
   }
   if (warp == 1) {
     tmem_alloc(&tmem_base_slot, TMEM_COLS);
@@ -105,6 +113,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
+  long long* stamps = p.dbg_times ? p.dbg_times + (static_cast<size_t>(blockIdx.y) * gridDim.x + blockIdx.x) * 8 : nullptr;
+  if (stamps && threadIdx.x == 0) { stamps[0] = clock64(); stamps[7] = static_cast<long long>(global_timer_ns()); }
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -115,18 +125,19 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(&empty_bar[s], ph ^ 1u);
         uint8_t* sa = ring_ptr + static_cast<size_t>(s) * p.stage_bytes;
         uint8_t* sb = sa + p.a_bytes;
+        if (p.debug & 1) { mbar_arrive(&full_bar[s]); continue; }
         mbar_expect_tx(&full_bar[s], p.a_bytes + p.b_bytes);
         const int k0 = (kb_begin + it) * BK;
         if (!A_MN) {
           tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
         } else {
 #pragma unroll
-          for (int b = 0; b < BM / 32; ++b) tma_load_2d(sa + b * 4096, &tmA, &full_bar[s], m0 + 32 * b, k0);
+          for (int b = 0; b < BM / 32; ++b) tma_load_2d(sa + b * (128 * BK), &tmA, &full_bar[s], m0 + 32 * b, k0);
         }
         if (!B_MN) {
           tma_load_2d(sb, &tmB, &full_bar[s], k0, n0);
         } else {
-          for (int b = 0; b < p.bn / 32; ++b) tma_load_2d(sb + b * 4096, &tmB, &full_bar[s], n0 + 32 * b, k0);
+          for (int b = 0; b < p.bn / 32; ++b) tma_load_2d(sb + b * (128 * BK), &tmB, &full_bar[s], n0 + 32 * b, k0);
         }
       }
     }
@@ -138,10 +149,15 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t tail_off = p.a_bytes + p.b_bytes;  // tails live right after the raw tiles
       // K-major: 8-row groups 1024 B apart (SW128). MN-major: 32-wide MN blocks 4096 B apart, 4-row
       // K groups 512 B apart (SW128 with 32-byte atoms: the only MN-major layout tf32 accepts).
-      const uint32_t a_lbo = A_MN ? 4096u : 16u, b_lbo = B_MN ? 4096u : 16u;
-      const uint32_t a_sbo = A_MN ? 512u : 1024u, b_sbo = B_MN ? 512u : 1024u;
-      const uint32_t a_lt = A_MN ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW128;
-      const uint32_t b_lt = B_MN ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW128;
+      // With BK = 16 a K-major row is 64 B: 64-byte swizzle, 8-row groups 512 B apart; an MN-major box
+      // then holds 16 K rows (2048 B).
+      constexpr uint32_t kmajor_sbo = 8u * BK * 4u;
+      constexpr uint32_t kmajor_lt = BK == 32 ? UMMA_LAYOUT_SW128 : UMMA_LAYOUT_SW64;
+      constexpr uint32_t mn_box = 128u * BK;
+      const uint32_t a_lbo = A_MN ? mn_box : 16u, b_lbo = B_MN ? mn_box : 16u;
+      const uint32_t a_sbo = A_MN ? 512u : kmajor_sbo, b_sbo = B_MN ? 512u : kmajor_sbo;
+      const uint32_t a_lt = A_MN ? UMMA_LAYOUT_SW128_BASE32B : kmajor_lt;
+      const uint32_t b_lt = B_MN ? UMMA_LAYOUT_SW128_BASE32B : kmajor_lt;
       const uint32_t a_kstep = A_MN ? 1024u : 32u, b_kstep = B_MN ? 1024u : 32u;
       for (int it = 0; it < n_iters; ++it) {
         const int s = it % p.stages;
@@ -150,6 +166,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tcgen05_fence_after();
         const uint32_t sa = ring + static_cast<uint32_t>(s) * p.stage_bytes;
         const uint32_t sb = sa + p.a_bytes;
+        if (p.debug & 2) { mbar_arrive(&empty_bar[s]); continue; }
         const int k_left = p.K - (kb_begin + it) * BK;
         const int ksteps = min(BK / UMMA_K, (k_left + UMMA_K - 1) / UMMA_K);
         for (int j = 0; j < ksteps; ++j) {
@@ -168,12 +185,18 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         tcgen05_commit(&empty_bar[s]);  // smem slot reusable once these MMAs have read it
       }
-      tcgen05_commit(&accum_bar);       // accumulators complete
+      if (p.debug & 2) mbar_arrive(&accum_bar);
+      else tcgen05_commit(&accum_bar);  // accumulators complete
+      if (stamps) stamps[2] = clock64();
     }
     __syncwarp();
   } else {
     // ------------------------------------------------------------------ splitter, then epilogue
     const int et = threadIdx.x - 64;  // 0..127
+    // bias slice of this tile -> smem once (zero beyond N), read back as warp-wide broadcasts
+    for (int j = et; j < MAX_BN; j += EPI_THREADS)
+      s_bias[j] = (p.bias != nullptr && j < p.bn && n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
+    named_bar_sync(1, EPI_THREADS);
     if (NSPLIT == 3) {
       const uint32_t raw_bytes = p.a_bytes + p.b_bytes;
       const int nvec = static_cast<int>(raw_bytes >> 4);
@@ -199,8 +222,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
 
+    if (stamps && et == 0) stamps[1] = clock64();
     mbar_wait(&accum_bar, 0);
     tcgen05_fence_after();
+    if (stamps && et == 0) stamps[3] = clock64();
 
     const int wq = warp & 3;                 // TMEM lane quarter this warp may read
     const int r_in_tile = wq * 32 + lane;
@@ -213,7 +238,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
     bool finalize = true;
     if (p.splits > 1) {
-      // write this split's partial tile; the last CTA to arrive for the tile sums them in split order
+      // split-K: park this split's partial tile in scratch; splitk_reduce_kernel sums the splits in
+      // order (deterministic) and applies the epilogue
       float* my = p.scratch + (static_cast<size_t>(tile) * p.splits + split) * (BM * MAX_BN);
       for (int c = 0; c < acc_chunks; ++c) {
         tmem_ld_32x32(taddr + c * 32, r);
@@ -224,63 +250,36 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
                                __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
       }
-      __threadfence();
-      named_bar_sync(1, EPI_THREADS);
-      if (et == 0) {
-        const unsigned int old = atomicAdd(&p.counters[tile], 1u);
-        last_flag = (old == static_cast<unsigned int>(p.splits - 1)) ? 1u : 0u;
-        if (last_flag) p.counters[tile] = 0u;  // leave the counter ready for the next launch
-      }
-      named_bar_sync(1, EPI_THREADS);
-      finalize = last_flag != 0u;
-      if (finalize) __threadfence();
+      finalize = false;
     }
 
     if (finalize) {
+      const bool has_drop = p.drop_thr16 != 0u;
+      const bool has_mask = p.mask_src != nullptr;
+      const bool relu = p.relu != 0;
       uint32_t step = p.step_imm;
-      if (p.drop_thr16 != 0u && p.step_ptr != nullptr) step = *p.step_ptr;
+      if (has_drop && p.step_ptr != nullptr) step = *p.step_ptr;
+      // TMA-store staging: two 32x32 fp32 boxes per warp at the start of the (now idle) stage ring
+      uint8_t* stage_buf = ring_ptr + static_cast<size_t>(wq) * 8192;
       for (int c = 0; c < n_chunks; ++c) {
         float v[32];
-        if (p.splits > 1) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = 0.f;
-          if (c < acc_chunks) {
-            for (int z = 0; z < p.splits; ++z) {
-              const float4* src = reinterpret_cast<const float4*>(
-                  p.scratch + (static_cast<size_t>(tile) * p.splits + z) * (BM * MAX_BN) +
-                  (static_cast<size_t>(c) * BM + r_in_tile) * 32);
-#pragma unroll
-              for (int q = 0; q < 8; ++q) {
-                const float4 t = __ldcg(src + q);
-                v[4 * q] += t.x; v[4 * q + 1] += t.y; v[4 * q + 2] += t.z; v[4 * q + 3] += t.w;
-              }
-            }
-          }
-        } else {
-          if (c < acc_chunks) {
-            tmem_ld_32x32(taddr + c * 32, r);
-            tmem_ld_wait();
-          }
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = (c < acc_chunks) ? __uint_as_float(r[j]) : 0.f;
+        if (c < acc_chunks) {
+          tmem_ld_32x32(taddr + c * 32, r);
+          tmem_ld_wait();
         }
-
-        const int col0 = n0 + c * 32;
-        // bias + ReLU
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = (c < acc_chunks) ? __uint_as_float(r[j]) : 0.f;
+        // TMEM columns past the MMA's N were never written: force them (and their bias) to zero.
+        // Columns between N and umma_n hold exact zeros already (TMA zero-fills out-of-range B rows).
+        const int live = static_cast<int>(umma_n) - c * 32;
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          const int col = col0 + j;
-          float x = v[j];
-          if (col < p.N) {
-            if (p.bias != nullptr) x += __ldg(p.bias + col);
-            if (p.relu) x = fmaxf(x, 0.f);
-          } else {
-            x = 0.f;
-          }
-          v[j] = x;
+          float x = (j < live) ? v[j] + s_bias[c * 32 + j] : 0.f;
+          v[j] = relu ? fmaxf(x, 0.f) : x;
         }
+        const int col0 = n0 + c * 32;
         // dropout: element index e = row*N + col, 8 elements per Philox call, 16 bits each
-        if (p.drop_thr16 != 0u && row < p.M) {
+        if (has_drop && row < p.M) {
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             const unsigned long long e0 =
@@ -306,14 +305,45 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
         // backward mask of the previous layer's ReLU+dropout output
-        if (p.mask_src != nullptr && row < p.M) {
+        if (has_mask && row < p.M) {
           const float* ms = p.mask_src + static_cast<size_t>(row) * p.ldm + col0;
+          if (col0 + 32 <= p.N && ((reinterpret_cast<uintptr_t>(ms) & 15u) == 0)) {
+            float4 mk[8];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            if (col0 + j < p.N) v[j] = (__ldg(ms + j) > 0.f) ? v[j] * p.mask_scale : 0.f;
+            for (int q = 0; q < 8; ++q) mk[q] = __ldg(reinterpret_cast<const float4*>(ms) + q);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              v[4 * q] = mk[q].x > 0.f ? v[4 * q] * p.mask_scale : 0.f;
+              v[4 * q + 1] = mk[q].y > 0.f ? v[4 * q + 1] * p.mask_scale : 0.f;
+              v[4 * q + 2] = mk[q].z > 0.f ? v[4 * q + 2] * p.mask_scale : 0.f;
+              v[4 * q + 3] = mk[q].w > 0.f ? v[4 * q + 3] * p.mask_scale : 0.f;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < p.N) v[j] = (__ldg(ms + j) > 0.f) ? v[j] * p.mask_scale : 0.f;
           }
         }
-        if (row < p.M) {
+        if (p.debug & 4) continue;
+        if (p.tma_store) {
+          // registers -> 128B-swizzled smem box -> one bulk tensor store per warp (clipped at the
+          // tensor edge by the TMA unit, full 128-byte lines on the wire)
+          uint8_t* buf = stage_buf + (c & 1) * 4096;
+          if (c >= 2) {
+            if (lane == 0) tma_store_wait_read<1>();  // the store issued two chunks ago has drained this box
+            __syncwarp();
+          }
+          uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            *reinterpret_cast<float4*>(rowp + ((q ^ (lane & 7)) << 4)) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmOut, buf, col0, m0 + wq * 32);
+            tma_store_commit();
+          }
+        } else if (row < p.M) {
           float* dst = p.out + static_cast<size_t>(row) * p.ldo + col0;
           const int rem = n_cols_out - c * 32;
           if (rem >= 32 && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0)) {
@@ -327,13 +357,57 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
       }
+      if (p.tma_store && lane == 0) tma_store_wait_all();  // smem must outlive the bulk reads
     }
   }
 
+  if (stamps && threadIdx.x == 64) stamps[4] = clock64();
   // teardown: all TMEM reads done before the allocating warp frees the columns
   tcgen05_fence_before();
   __syncthreads();
+  if (stamps && threadIdx.x == 0) { stamps[5] = clock64(); stamps[6] = static_cast<long long>(global_timer_ns()); }
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// Sums the split-K partial tiles (in split order, so the result is reproducible) and writes the
+// output with bias / ReLU applied. One block = 32 rows x 32 columns of one tile chunk; thread =
+// one float4, so both the scratch reads and the output writes are full 128-byte lines.
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const float* __restrict__ scratch, int splits, int m_tiles, int bn, int M, int N, int n_store,
+                     float* __restrict__ out, int ldo, const float* __restrict__ bias, int relu) {
+  const int chunks = (bn + 31) / 32;
+  const int tile = blockIdx.x / chunks, c = blockIdx.x % chunks;
+  const int m_tile = tile % m_tiles, n_tile = tile / m_tiles;
+  const int r = blockIdx.y * 32 + (threadIdx.x >> 3), q = threadIdx.x & 7;
+  const int row = m_tile * BM + r;
+  const int col = n_tile * bn + c * 32 + q * 4;
+  if (row >= M || col >= n_store || c * 32 + q * 4 >= bn) return;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float* src = scratch + (static_cast<size_t>(tile) * splits) * (BM * MAX_BN) + (static_cast<size_t>(c) * BM + r) * 32 + q * 4;
+  if (col < N) {
+    for (int z = 0; z < splits; ++z) {
+      const float4 t = __ldcg(reinterpret_cast<const float4*>(src + static_cast<size_t>(z) * (BM * MAX_BN)));
+      acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+    }
+  }
+  float v[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    float x = 0.f;
+    if (col + j < N) {
+      x = v[j] + (bias != nullptr ? __ldg(bias + col + j) : 0.f);
+      if (relu) x = fmaxf(x, 0.f);
+    }
+    v[j] = x;
+  }
+  float* dst = out + static_cast<size_t>(row) * ldo + col;
+  if (col + 3 < n_store && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0)) {
+    *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (col + j < n_store) dst[j] = v[j];
+  }
 }
 
 // ------------------------------------------------------------------------------------ host side
@@ -356,7 +430,7 @@ static EncodeTiledFn get_encode_fn() {
 
 // 2-D fp32 tensor map over a row-major [outer, inner] matrix with leading dimension ld (elements).
 static int make_map(CUtensorMap* map, const float* base, int inner, int outer, int ld, int box_inner, int box_outer,
-                    bool mn_major) {
+                    CUtensorMapSwizzle swizzle) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) return fail(RTDC_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
   if ((reinterpret_cast<uintptr_t>(base) & 15u) != 0) return fail(RTDC_ERR_ARG, "operand pointer must be 16-byte aligned");
@@ -366,7 +440,7 @@ static int make_map(CUtensorMap* map, const float* base, int inner, int outer, i
   cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(RTDC_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
@@ -374,6 +448,7 @@ static int make_map(CUtensorMap* map, const float* base, int inner, int outer, i
 }
 
 struct Plan {
+  int bk;
   int bn, stages, splits, kb_per_split, num_kb, m_tiles, n_tiles;
   uint32_t a_bytes, b_bytes, stage_bytes;
   size_t smem;
@@ -406,50 +481,52 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
   pl->n_tiles = ceil_div(d->N, bn);
   if (d->n_store > d->N && d->n_store > pl->n_tiles * bn)
     return fail(RTDC_ERR_ARG, "n_store (%d) reaches beyond the last N tile", d->n_store);
-  pl->num_kb = ceil_div(d->K, BK);
-  pl->a_bytes = BM * BK * 4;
-  pl->b_bytes = static_cast<uint32_t>(bn) * BK * 4;
+  pl->bk = d->precision == 3 ? 16 : 32;
+  pl->num_kb = ceil_div(d->K, pl->bk);
+  pl->a_bytes = BM * pl->bk * 4;
+  pl->b_bytes = static_cast<uint32_t>(bn) * pl->bk * 4;
   pl->stage_bytes = (pl->a_bytes + pl->b_bytes) * (d->precision == 3 ? 2u : 1u);
-  int stages = static_cast<int>((SMEM_LIMIT - 1024 - 256) / pl->stage_bytes);
+  int stages = static_cast<int>((SMEM_LIMIT - STATIC_SMEM_RESERVE - 1024) / pl->stage_bytes);
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages > pl->num_kb) stages = pl->num_kb < 1 ? 1 : pl->num_kb;
   if (stages < 1) return fail(RTDC_ERR_LIMIT, "tile does not fit shared memory");
   pl->stages = stages;
-  pl->smem = static_cast<size_t>(stages) * pl->stage_bytes + 1024;
+  pl->smem = static_cast<size_t>(stages) * pl->stage_bytes;
+  if (pl->smem < 32768) pl->smem = 32768;  // the epilogue stages its TMA stores in the idle ring (4 warps x 8 KB)
+  pl->smem += 1024;
   const int tiles = pl->m_tiles * pl->n_tiles;
   int splits = d->splits;
   if (splits == 0) {
     splits = 1;
     const int sms = need_device ? num_sms() : 148;
-    if (tiles * 2 <= sms && pl->num_kb >= 16) {
+    if (tiles * 2 <= sms && d->K >= 512 && d->drop_p <= 0.f && d->mask_src == nullptr) {
       splits = sms / tiles;
-      const int max_by_k = pl->num_kb / 8;  // keep >= 8 K blocks per split
+      const int max_by_k = d->K / 256;  // keep >= 256 K elements per split
       if (splits > max_by_k) splits = max_by_k;
       if (splits > 64) splits = 64;
       if (splits < 1) splits = 1;
     }
   }
+  if (splits > 1 && (d->drop_p > 0.f || d->mask_src != nullptr)) splits = 1;  // those epilogues need the full sum in TMEM
   if (splits > pl->num_kb) splits = pl->num_kb;
   pl->kb_per_split = ceil_div(pl->num_kb, splits);
   pl->splits = ceil_div(pl->num_kb, pl->kb_per_split);  // no empty split
   return RTDC_OK;
 }
 
-// scratch layout: [COUNTER_BYTES of per-tile arrival counters][tiles x splits partial tiles]. The
-// counters sit at a fixed place so one buffer can serve differently shaped calls one after another.
-constexpr size_t COUNTER_BYTES = 4096;
+// scratch layout: [tiles x splits] partial tiles of BM x MAX_BN floats, chunk-major inside a tile
 static size_t scratch_bytes_for(const Plan& pl) {
   if (pl.splits <= 1) return 0;
   const size_t tiles = static_cast<size_t>(pl.m_tiles) * pl.n_tiles;
-  return COUNTER_BYTES + tiles * pl.splits * (static_cast<size_t>(BM) * MAX_BN * 4);
+  return tiles * pl.splits * (static_cast<size_t>(BM) * MAX_BN * 4);
 }
 
-template <bool A_MN, bool B_MN, int NSPLIT>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& gp, const Plan& pl, cudaStream_t st) {
-  auto kern = gemm_tf32_kernel<A_MN, B_MN, NSPLIT>;
-  RTDC_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT - 1024));
+template <bool A_MN, bool B_MN, int NSPLIT, int BK>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const GemmParams& gp, const Plan& pl, cudaStream_t st) {
+  auto kern = gemm_tf32_kernel<A_MN, B_MN, NSPLIT, BK>;
+  RTDC_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT - STATIC_SMEM_RESERVE));
   dim3 grid(pl.m_tiles * pl.n_tiles, pl.splits, 1);
-  kern<<<grid, NUM_THREADS, pl.smem, st>>>(ta, tb, gp);
+  kern<<<grid, NUM_THREADS, pl.smem, st>>>(ta, tb, to, gp);
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;
 }
@@ -473,6 +550,9 @@ RTDC_API int rtdc_gemm_plan(const rtdc_gemm_desc* d, int* out5) {
   return RTDC_OK;
 }
 
+static int dispatch(const rtdc_gemm_desc* d, bool three, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
+                    const rtdc::GemmParams& gp, const rtdc::Plan& pl, cudaStream_t st);
+
 RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   Plan pl;
   int rc = make_plan(d, &pl, true);
@@ -483,11 +563,13 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   if (d->ldo < n_store) return fail(RTDC_ERR_ARG, "ldo (%d) smaller than the stored width (%d)", d->ldo, n_store);
 
   CUtensorMap ta, tb;
-  if (!d->a_mn) rc = make_map(&ta, d->a, d->K, d->M, d->lda, BK, BM, false);
-  else          rc = make_map(&ta, d->a, d->M, d->K, d->lda, 32, BK, true);
+  const CUtensorMapSwizzle sw_k = pl.bk == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  const CUtensorMapSwizzle sw_mn = CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B;
+  if (!d->a_mn) rc = make_map(&ta, d->a, d->K, d->M, d->lda, pl.bk, BM, sw_k);
+  else          rc = make_map(&ta, d->a, d->M, d->K, d->lda, 32, pl.bk, sw_mn);
   if (rc != RTDC_OK) return rc;
-  if (!d->b_mn) rc = make_map(&tb, d->b, d->K, d->N, d->ldb, BK, pl.bn, false);
-  else          rc = make_map(&tb, d->b, d->N, d->K, d->ldb, 32, BK, true);
+  if (!d->b_mn) rc = make_map(&tb, d->b, d->K, d->N, d->ldb, pl.bk, pl.bn, sw_k);
+  else          rc = make_map(&tb, d->b, d->N, d->K, d->ldb, 32, pl.bk, sw_mn);
   if (rc != RTDC_OK) return rc;
 
   GemmParams gp;
@@ -512,15 +594,37 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
     const size_t need = scratch_bytes_for(pl);
     if (!d->scratch || d->scratch_bytes < need)
       return fail(RTDC_ERR_ARG, "split-K x%d needs %zu bytes of scratch (got %zu)", pl.splits, need, d->scratch_bytes);
-    if (static_cast<size_t>(pl.m_tiles) * pl.n_tiles * 4 > COUNTER_BYTES)
-      return fail(RTDC_ERR_LIMIT, "split-K supports at most %zu output tiles", COUNTER_BYTES / 4);
-    gp.counters = reinterpret_cast<unsigned int*>(d->scratch);
-    gp.scratch = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(d->scratch) + COUNTER_BYTES);
+    gp.scratch = d->scratch;
   }
+  // output through TMA stores when the destination allows a tensor map (16-byte aligned base and
+  // row pitch); otherwise the epilogue falls back to direct per-thread stores
+  CUtensorMap to;
+  memset(&to, 0, sizeof(to));
+  if ((reinterpret_cast<uintptr_t>(d->out) & 15u) == 0 && (static_cast<size_t>(d->ldo) * 4) % 16 == 0 &&
+      !getenv("RTDC_GEMM_NO_TMA_STORE")) {
+    rc = make_map(&to, d->out, n_store, d->M, d->ldo, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc != RTDC_OK) return rc;
+    gp.tma_store = 1;
+  }
+  if (const char* dbg = getenv("RTDC_GEMM_DEBUG")) gp.debug = atoi(dbg);
+  if (const char* dbg = getenv("RTDC_GEMM_DEBUG_BUF")) gp.dbg_times = reinterpret_cast<long long*>(strtoull(dbg, nullptr, 0));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool three = d->precision == 3;
-  if (!d->a_mn && !d->b_mn) return three ? launch<false, false, 3>(ta, tb, gp, pl, st) : launch<false, false, 1>(ta, tb, gp, pl, st);
-  if (!d->a_mn && d->b_mn)  return three ? launch<false, true, 3>(ta, tb, gp, pl, st)  : launch<false, true, 1>(ta, tb, gp, pl, st);
-  if (d->a_mn && !d->b_mn)  return three ? launch<true, false, 3>(ta, tb, gp, pl, st)  : launch<true, false, 1>(ta, tb, gp, pl, st);
-  return three ? launch<true, true, 3>(ta, tb, gp, pl, st) : launch<true, true, 1>(ta, tb, gp, pl, st);
+  rc = dispatch(d, three, ta, tb, to, gp, pl, st);
+  if (rc != RTDC_OK) return rc;
+  if (pl.splits > 1) {
+    dim3 grid(pl.m_tiles * pl.n_tiles * ((pl.bn + 31) / 32), BM / 32);
+    splitk_reduce_kernel<<<grid, 256, 0, st>>>(gp.scratch, pl.splits, pl.m_tiles, pl.bn, d->M, d->N, n_store, d->out, d->ldo,
+                                              d->bias, d->relu);
+    RTDC_CUDA_CHECK(cudaGetLastError());
+  }
+  return RTDC_OK;
+}
+
+static int dispatch(const rtdc_gemm_desc* d, bool three, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
+                    const rtdc::GemmParams& gp, const rtdc::Plan& pl, cudaStream_t st) {
+  if (!d->a_mn && !d->b_mn) return three ? launch<false, false, 3, 16>(ta, tb, to, gp, pl, st) : launch<false, false, 1, 32>(ta, tb, to, gp, pl, st);
+  if (!d->a_mn && d->b_mn)  return three ? launch<false, true, 3, 16>(ta, tb, to, gp, pl, st)  : launch<false, true, 1, 32>(ta, tb, to, gp, pl, st);
+  if (d->a_mn && !d->b_mn)  return three ? launch<true, false, 3, 16>(ta, tb, to, gp, pl, st)  : launch<true, false, 1, 32>(ta, tb, to, gp, pl, st);
+  return three ? launch<true, true, 3, 16>(ta, tb, to, gp, pl, st) : launch<true, true, 1, 32>(ta, tb, to, gp, pl, st);
 }

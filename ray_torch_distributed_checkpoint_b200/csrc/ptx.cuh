@@ -87,6 +87,19 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* m, uin
       : "memory");
 }
 
+// 2-D tiled store shared -> global (clipped at the tensor bounds), tracked by bulk async-groups.
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(m),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // ---------------------------------------------------------------- TMEM / tcgen05
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_in_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_in_smem)),
@@ -112,7 +125,7 @@ __device__ __forceinline__ void tcgen05_commit(uint64_t* bar) {
 //                     (tf32) MN-major operands must use the 128B swizzle with 32-byte atomicity
 //                     (layout type 1; atom = 128 B x 4 K rows = 512 B, Swizzle<2,5,2> on the byte
 //                     address), matching TMA's CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
-enum : uint32_t { UMMA_LAYOUT_SW128 = 2, UMMA_LAYOUT_SW128_BASE32B = 1 };
+enum : uint32_t { UMMA_LAYOUT_SW128 = 2, UMMA_LAYOUT_SW128_BASE32B = 1, UMMA_LAYOUT_SW64 = 4 };
 __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
                                                    uint32_t layout_type = UMMA_LAYOUT_SW128) {
   uint64_t d = 0;

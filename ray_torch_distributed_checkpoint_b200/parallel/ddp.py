@@ -1,0 +1,225 @@
+"""Data-parallel wrapper: flat parameter / gradient arenas, bucketed all-reduce overlapped with
+backward, rank-0 parameter broadcast.
+
+This is the framework's replacement for ``torch.nn.parallel.DistributedDataParallel`` as applied by
+``ray.train.torch.prepare_model`` (``/root/reference/my_ray_module.py:135``):
+
+* wrap time (C2): parameters are moved into one flat arena and made bit-identical to rank 0's;
+* backward (C3): gradients live in a flat arena laid out bucket by bucket (``buckets.plan``). On GPU
+  that arena is peer-mapped symmetric memory, and as soon as the last gradient of a bucket has been
+  produced the bucket is reduced by the hand-written NVLink kernel (``csrc/allreduce.cu``: two-shot
+  P2P or NVLS multimem, ``x 1/world`` fused) on a side stream while backward continues;
+* ``state_dict()`` keys carry the ``module.`` prefix exactly like DDP's, which is why the reference
+  strips it on load (``my_ray_module.py:261``).
+
+On CPU workers (``use_gpu=False``, the gloo configuration) the same wrapper reduces each bucket with
+``torch.distributed.all_reduce``.
+"""
+from __future__ import annotations
+
+import contextlib
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from . import buckets as _buckets
+
+
+class _C10dComm:
+    """Bucket reduction through torch.distributed (gloo on CPU workers)."""
+
+    def __init__(self, grad_arena: torch.Tensor, group=None):
+        self.arena = grad_arena
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self._works = []
+
+    def reduce_bucket(self, bucket: _buckets.Bucket):
+        view = self.arena[bucket.offset:bucket.offset + bucket.numel]
+        view.div_(self.world)
+        self._works.append(dist.all_reduce(view, group=self.group, async_op=True))
+
+    def finish(self):
+        for w in self._works:
+            w.wait()
+        self._works.clear()
+
+    def broadcast_(self, flat: torch.Tensor, src: int = 0):
+        dist.broadcast(flat, src=src, group=self.group)
+
+
+class _SymmComm:
+    """Bucket reduction with our NVLink kernels over a SymmetricArena holding the gradient arena."""
+
+    def __init__(self, arena, grad_offset_bytes: int, element_size: int, dtype: torch.dtype, algo: str = "auto"):
+        self.arena = arena
+        self.grad_offset = grad_offset_bytes
+        self.esize = element_size
+        self.dtype = dtype
+        self.algo = algo
+        self.world = arena.world
+        self.stream = torch.cuda.Stream(arena.device)
+        self._pending = False
+
+    def reduce_bucket(self, bucket: _buckets.Bucket):
+        cur = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(cur)                       # the bucket's gradients are complete at this point of backward
+        self.stream.wait_event(ev)
+        self.arena.all_reduce(self.grad_offset + bucket.offset * self.esize, bucket.numel, dtype=self.dtype,
+                              scale=1.0 / self.world, algo=self.algo, stream=self.stream)
+        self._pending = True
+
+    def finish(self):
+        if self._pending:
+            torch.cuda.current_stream().wait_stream(self.stream)
+            self._pending = False
+
+    def broadcast_(self, flat: torch.Tensor, src: int = 0):
+        """Make ``flat`` equal to rank ``src``'s copy, staged through the (currently unused) gradient arena."""
+        nbytes = flat.numel() * flat.element_size()
+        stage = self.arena.tensor(self.grad_offset, flat.numel(), flat.dtype)
+        if self.arena.rank == src:
+            stage.copy_(flat)
+        self.arena.broadcast(self.grad_offset, nbytes, src, flat)
+        torch.cuda.current_stream().synchronize()
+        stage.zero_()
+
+
+class DistributedDataParallel(nn.Module):
+    """DDP over flat arenas. ``module`` keeps its parameters (re-pointed into the arena)."""
+
+    def __init__(self, module: nn.Module, *, device: Optional[torch.device] = None, process_group=None,
+                 bucket_cap_mb: float = 25.0, first_bucket_mb: float = 1.0, broadcast_buffers: bool = True,
+                 comm: str = "auto", algo: str = "auto"):
+        super().__init__()
+        if not dist.is_initialized():
+            raise RuntimeError("DistributedDataParallel needs an initialised process group")
+        self.module = module
+        self.process_group = process_group
+        self.world_size = dist.get_world_size(process_group)
+        self.rank = dist.get_rank(process_group)
+        self.broadcast_buffers = broadcast_buffers
+        self.require_backward_grad_sync = True
+        params = [(n, p) for n, p in module.named_parameters() if p.requires_grad]
+        if not params:
+            raise ValueError("module has no trainable parameters")
+        dtypes = {p.dtype for _, p in params}
+        if len(dtypes) != 1:
+            raise ValueError(f"all trainable parameters must share one dtype (got {dtypes})")
+        self.dtype = dtypes.pop()
+        dev = torch.device(device) if device is not None else params[0][1].device
+        self.device = dev
+        esize = params[0][1].element_size()
+        self.buckets, total = _buckets.plan(params, int(first_bucket_mb * 1024 * 1024), int(bucket_cap_mb * 1024 * 1024), esize)
+        self.total_elements = total
+
+        use_symm = dev.type == "cuda" and comm in ("auto", "symm") and self.dtype in (torch.float32, torch.bfloat16)
+        self.param_arena = torch.zeros(total, dtype=self.dtype, device=dev)
+        if use_symm:
+            from .symm import SymmetricArena
+            self.symm = SymmetricArena(total * esize + 4096, device=dev, group=process_group)
+            goff, self.grad_arena = self.symm.alloc(total, self.dtype)
+            self.comm = _SymmComm(self.symm, goff, esize, self.dtype, algo)
+        else:
+            self.symm = None
+            self.grad_arena = torch.zeros(total, dtype=self.dtype, device=dev)
+            self.comm = _C10dComm(self.grad_arena, process_group)
+
+        # re-point parameters and gradients into the arenas
+        by_name = dict(params)
+        self._slots: Dict[str, _buckets.ParamSlot] = {}
+        self._grad_views: Dict[int, torch.Tensor] = {}
+        self._bucket_of: Dict[int, int] = {}
+        with torch.no_grad():
+            for b in self.buckets:
+                for s in b.slots:
+                    p = by_name[s.name]
+                    pv = self.param_arena[s.offset:s.offset + s.numel].view(s.shape)
+                    pv.copy_(p.data)
+                    p.data = pv
+                    gv = self.grad_arena[s.offset:s.offset + s.numel].view(s.shape)
+                    p.grad = gv
+                    self._slots[s.name] = s
+                    self._grad_views[id(p)] = gv
+                    self._bucket_of[id(p)] = b.index
+        self._params = [by_name[s.name] for b in self.buckets for s in b.slots]
+        self._bucket_size = [len(b.slots) for b in self.buckets]
+        self._ready = [0] * len(self.buckets)
+        self._callback_queued = False
+        self._hooks = [p.register_post_accumulate_grad_hook(self._make_hook(p)) for p in self._params]
+
+        # C2: every replica starts from rank 0's parameters (and buffers)
+        self.comm.broadcast_(self.param_arena, src=0)
+        self._sync_buffers()
+
+    # ------------------------------------------------------------------------------------------
+    def _make_hook(self, p: torch.nn.Parameter):
+        pid = id(p)
+
+        def hook(param):
+            view = self._grad_views[pid]
+            g = param.grad
+            if g is not None and g.data_ptr() != view.data_ptr():
+                # the optimizer set grads to None (zero_grad default) and autograd allocated a fresh
+                # tensor: move it into the bucket and keep the bucket view as .grad from now on
+                view.copy_(g)
+                param.grad = view
+            if not self.require_backward_grad_sync:
+                return
+            b = self._bucket_of[pid]
+            self._ready[b] += 1
+            if not self._callback_queued:
+                torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
+                self._callback_queued = True
+            if self._ready[b] == self._bucket_size[b]:
+                self.comm.reduce_bucket(self.buckets[b])
+        return hook
+
+    def _finalize_backward(self):
+        self._callback_queued = False
+        # buckets whose parameters got no gradient this step (unused parameters) still take part
+        for b, n in enumerate(self._ready):
+            if 0 < n < self._bucket_size[b]:
+                self.comm.reduce_bucket(self.buckets[b])
+        self._ready = [0] * len(self.buckets)
+        self.comm.finish()
+
+    def _sync_buffers(self):
+        bufs = [b for b in self.module.buffers() if b.numel() > 0]
+        if not bufs or self.world_size == 1:
+            return
+        for b in bufs:                       # C4: ResNet-style running stats follow rank 0
+            if b.is_floating_point() or b.dtype in (torch.int64, torch.int32):
+                dist.broadcast(b, src=0, group=self.process_group)
+
+    # ------------------------------------------------------------------------------------------
+    def forward(self, *args, **kwargs):
+        if self.broadcast_buffers and self.training and self.require_backward_grad_sync:
+            self._sync_buffers()
+        return self.module(*args, **kwargs)
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        """Accumulate gradients locally; the next backward outside this context reduces the sum."""
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    def zero_grad(self, set_to_none: bool = False):
+        """Zero the whole gradient arena with one memset (``set_to_none`` is ignored: gradients stay
+        bucket views so that they are produced in place for the all-reduce)."""
+        self.grad_arena.zero_()
+        for p in self._params:
+            p.grad = self._grad_views[id(p)]
+
+    def flat_parameters(self) -> torch.Tensor:
+        return self.param_arena
+
+    def flat_gradients(self) -> torch.Tensor:
+        return self.grad_arena

@@ -1,0 +1,26 @@
+"""Component timing of the GEMM kernel with RTDC_GEMM_DEBUG bits (1 no TMA, 2 no MMA, 4 no stores)."""
+import os, sys, json
+import torch
+from ray_torch_distributed_checkpoint_b200 import ops
+B = 16384
+dev = "cuda"
+x = torch.randn(B, 784, device=dev); w1 = torch.randn(512, 784, device=dev) * .03; b1 = torch.randn(512, device=dev)
+out = torch.empty(B, 512, device=dev)
+def t(fn, n=10):
+    for _ in range(3): fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            for _ in range(n): fn()
+        g.replay(); s.synchronize()
+        a.record(s); g.replay(); b.record(s); s.synchronize()
+    return a.elapsed_time(b) / n * 1000
+for prec in (1, 3):
+    for bn in (256, 128):
+        for dbg in (0, 1, 2, 4, 5, 6, 3):
+            os.environ["RTDC_GEMM_DEBUG"] = str(dbg)
+            us = t(lambda: ops.gemm(x, w1, out, bias=b1, relu=True, precision=prec, bn=bn))
+            print(f"prec={prec} bn={bn} debug={dbg}: {us:.1f} us", flush=True)
