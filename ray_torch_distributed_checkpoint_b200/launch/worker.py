@@ -17,18 +17,9 @@ def main(payload_path: str) -> int:
     import pickle
 
     with open(payload_path, "rb") as f:
-        head = f.read()
-    # make the driver's import roots visible before unpickling user code
-    # (sys_path is stored in the payload itself, so peek with a tolerant first pass)
-    try:
-        payload = pickle.loads(head)
-    except ModuleNotFoundError:
-        payload = None
-    if payload is None:
-        sys.path.insert(0, os.getcwd())
-        payload = pickle.loads(head)
+        payload = pickle.load(f)      # the driver put its import roots on our PYTHONPATH
     for p in payload.get("sys_path", []):
-        if p not in sys.path:
+        if p and p not in sys.path:
             sys.path.append(p)
 
     from ..train.link import SocketLink
@@ -53,8 +44,10 @@ def main(payload_path: str) -> int:
         ctx = TrainContext(rank, world, local_rank, int(os.environ.get("LOCAL_WORLD_SIZE", world)),
                            int(os.environ.get("NODE_RANK", 0)), payload["experiment_name"], payload["trial_name"],
                            storage.trial_path, storage, use_gpu, payload.get("metadata"))
-        _set_session(_Session(ctx, link, payload.get("start_checkpoint"), payload.get("start_index", 0)))
+        session = _Session(ctx, link, payload.get("start_checkpoint"), payload.get("start_index", 0))
+        _set_session(session)
         _call_train_fn(payload["fn"], payload["config"])
+        session.drain()
         if use_gpu:
             torch.cuda.synchronize()
         from ..ckpt import async_writer

@@ -50,12 +50,39 @@ class _Session:
         self.report_index = start_index
         self.lock = threading.Lock()
 
-    def report(self, metrics: Dict[str, Any], checkpoint: Optional[Checkpoint] = None):
+    def report(self, metrics: Dict[str, Any], checkpoint=None, asynchronous: bool = False):
         if not isinstance(metrics, dict):
             raise TypeError("report(metrics=...) must be a dict")
-        ctx = self.context
+        self.drain()                      # at most one report in flight; keeps indices ordered
         idx = self.report_index
+        self.report_index += 1
+        if asynchronous:
+            def run():
+                try:
+                    self._do_report(idx, metrics, checkpoint)
+                except BaseException as e:   # surfaced by the next report()/drain()
+                    self._pending_error = e
+            self._pending = threading.Thread(target=run, name="rtdc-report", daemon=True)
+            self._pending.start()
+            return
+        self._do_report(idx, metrics, checkpoint)
+
+    def drain(self):
+        """Wait for an asynchronous report (checkpoint write + persist + driver barrier) to finish."""
+        t = getattr(self, "_pending", None)
+        if t is not None:
+            t.join()
+            self._pending = None
+        err = getattr(self, "_pending_error", None)
+        if err is not None:
+            self._pending_error = None
+            raise err
+
+    def _do_report(self, idx: int, metrics: Dict[str, Any], checkpoint):
+        ctx = self.context
         persisted_path = None
+        if checkpoint is not None and hasattr(checkpoint, "result") and not isinstance(checkpoint, Checkpoint):
+            checkpoint = checkpoint.result()          # ckpt.PendingCheckpoint: wait for the writer thread
         if checkpoint is not None:
             storage = ctx.get_storage()
             t0 = time.time()
@@ -67,8 +94,7 @@ class _Session:
         self.link.report(rank=ctx.get_world_rank(), index=idx, metrics=metrics, checkpoint_path=persisted_path)
         if self.link.any_checkpoint(idx):
             self.latest_checkpoint = Checkpoint.from_directory(ctx.get_storage().checkpoint_path(idx))
-        self.report_index += 1
-        _maybe_inject_fault(ctx.get_world_rank(), self.report_index)
+        _maybe_inject_fault(ctx.get_world_rank(), idx + 1)
 
 
 _session: Optional[_Session] = None
@@ -89,14 +115,22 @@ def in_session() -> bool:
     return _session is not None
 
 
-def report(metrics: Dict[str, Any], *, checkpoint: Optional[Checkpoint] = None) -> None:
+def report(metrics: Dict[str, Any], *, checkpoint=None, checkpoint_upload_mode: str = "sync") -> None:
     """Report metrics (and optionally a checkpoint directory) for this step/epoch.
 
     Must be called by every worker the same number of times. The checkpoint's files are persisted to
-    ``<storage_path>/<experiment>/<trial>/checkpoint_{index:06d}/`` and the call returns once all
-    workers have reported and retention (``CheckpointConfig.num_to_keep``) has been applied.
+    ``<storage_path>/<experiment>/<trial>/checkpoint_{index:06d}/`` and, in the default ``"sync"`` mode,
+    the call returns once all workers have reported and retention (``CheckpointConfig.num_to_keep``)
+    has been applied.
+
+    ``checkpoint`` may be a ``Checkpoint`` or a ``ckpt.PendingCheckpoint`` (files still being written
+    by the asynchronous checkpointer). With ``checkpoint_upload_mode="async"`` — pass it on every rank
+    — waiting for the writer, persisting and the cross-worker barrier all happen on a background
+    thread while training continues; the next ``report`` (or the end of the loop) waits for it.
     """
-    _get_session("report").report(metrics, checkpoint)
+    if checkpoint_upload_mode not in ("sync", "async"):
+        raise ValueError("checkpoint_upload_mode must be 'sync' or 'async'")
+    _get_session("report").report(metrics, checkpoint, asynchronous=checkpoint_upload_mode == "async")
 
 
 def get_checkpoint() -> Optional[Checkpoint]:
@@ -105,7 +139,9 @@ def get_checkpoint() -> Optional[Checkpoint]:
     After a worker-group restart (``FailureConfig.max_failures``) or when the trainer was given
     ``resume_from_checkpoint``, this is where the training function finds its starting state.
     """
-    return _get_session("get_checkpoint").latest_checkpoint
+    s = _get_session("get_checkpoint")
+    s.drain()
+    return s.latest_checkpoint
 
 
 def get_context() -> TrainContext:

@@ -174,7 +174,9 @@ class TorchTrainer:
                 "experiment_name": storage.experiment_name, "trial_name": storage.trial_name,
             }, f)
         server = DriverServer(sock, sc.num_workers, authkey)
-        group = WorkerGroup(sc.num_workers, worker_argv(payload), env={"RTDC_ATTEMPT": str(attempt)})
+        # workers must be able to import whatever module the training function lives in
+        py_path = os.pathsep.join([p for p in sys.path if p] + [os.environ.get("PYTHONPATH", "")]).strip(os.pathsep)
+        group = WorkerGroup(sc.num_workers, worker_argv(payload), env={"RTDC_ATTEMPT": str(attempt), "PYTHONPATH": py_path})
         group.start()
         pending: Dict[int, List[dict]] = {}
         done_ranks, hello_ranks = set(), set()
@@ -273,10 +275,12 @@ class TorchTrainer:
         ctx = TrainContext(rank, world, local_rank, int(os.environ.get("LOCAL_WORLD_SIZE", world)),
                            int(os.environ.get("NODE_RANK", 0)), storage.experiment_name, storage.trial_name,
                            storage.trial_path, storage, sc.use_gpu, self.metadata)
-        _set_session(_Session(ctx, link, self.resume_from_checkpoint))
+        session = _Session(ctx, link, self.resume_from_checkpoint)
+        _set_session(session)
         error = None
         try:
             _call_train_fn(self.train_loop_per_worker, self.train_loop_config)
+            session.drain()
         except Exception as e:     # surface through Result like the driver mode does
             error = e
             raise
