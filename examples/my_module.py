@@ -42,6 +42,14 @@ _TEST_SIZE = int(os.environ.get("RTDC_TEST_SIZE", 10000))
 def get_dataloaders(batch_size, val_only=False, as_ray_ds=False):
     """Train/validation loaders (or ``data.Dataset`` objects with ``as_ray_ds=True``) over the synthetic
     FashionMNIST-shape data; ``val_only=True`` returns just the test split (ref my_ray_module.py:30-76)."""
+    real = _real_fashion_mnist()
+    if real is not None:
+        training, test = real
+        if val_only:
+            return _as_ds(test) if as_ray_ds else DataLoader(test, batch_size=batch_size)
+        if as_ray_ds:
+            return _as_ds(training), _as_ds(test)
+        return DataLoader(training, batch_size=batch_size, shuffle=True), DataLoader(test, batch_size=batch_size)
     test = data.FashionMNISTSynthetic(train=False, size=_TEST_SIZE)
     if val_only:
         if as_ray_ds:
@@ -52,6 +60,25 @@ def get_dataloaders(batch_size, val_only=False, as_ray_ds=False):
         return (data.from_numpy({"features": training.normalized().numpy(), "labels": training.targets.numpy()}),
                 data.from_numpy({"features": test.normalized().numpy(), "labels": test.targets.numpy()}))
     return DataLoader(training, batch_size=batch_size, shuffle=True), DataLoader(test, batch_size=batch_size)
+
+
+def _real_fashion_mnist():
+    """The real dataset when it is already on disk under ~/data (there is no network to download it).
+    Guarded by the same file lock the reference uses so co-located workers do not race (ref :41,54)."""
+    root = os.path.expanduser("~/data")
+    if os.environ.get("RTDC_SYNTHETIC_DATA") or not os.path.isdir(os.path.join(root, "FashionMNIST", "raw")):
+        return None
+    from filelock import FileLock
+    from torchvision import datasets, transforms
+    tf = transforms.Compose([transforms.ToTensor(), transforms.Normalize((0.5,), (0.5,))])
+    with FileLock(os.path.expanduser("~/data.lock")):
+        return (datasets.FashionMNIST(root=root, train=True, download=False, transform=tf),
+                datasets.FashionMNIST(root=root, train=False, download=False, transform=tf))
+
+
+def _as_ds(torch_dataset):
+    xs = ((torch_dataset.data.to(torch.float32) / 255.0 - 0.5) / 0.5).unsqueeze(1).numpy()
+    return data.from_numpy({"features": xs, "labels": torch_dataset.targets.numpy()})
 
 
 get_labels_map = data.get_labels_map

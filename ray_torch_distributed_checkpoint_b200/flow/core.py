@@ -351,6 +351,22 @@ class _GpuSampler:
         self._thread.join(timeout=2.0)
 
 
+def _gpu_profile_card(samples: List[Dict[str, Any]]):
+    """Attach the sampler's series to the task as the ``gpu_profile`` card (peak / mean per GPU)."""
+    from .cards import Markdown, Table
+    c = current.card["gpu_profile"]
+    c.append(Markdown(f"### GPU profile ({len(samples)} samples)"))
+    if not samples:
+        c.append(Markdown("no NVML device visible to this task"))
+        return
+    keys = sorted(k for k in samples[-1] if k != "t")
+    rows = []
+    for k in keys:
+        vals = [s[k] for s in samples if k in s]
+        rows.append([k, f"{sum(vals) / len(vals):.1f}", f"{max(vals):.1f}"])
+    c.append(Table(headers=["series", "mean", "max"], data=rows))
+
+
 # ------------------------------------------------------------------------------------------------ FlowSpec
 class _Inputs(list):
     """``inputs`` of a join step: iterable of per-task namespaces; attribute access picks by step name."""
@@ -462,6 +478,7 @@ class FlowSpec:
                     sampler.stop()
                     with open(os.path.join(task_dir, "gpu_profile.json"), "w") as f:
                         json.dump(sampler.samples, f)
+                    _gpu_profile_card(sampler.samples)
         arts = self._artifacts() if execute_body else {}
         with open(os.path.join(task_dir, "artifacts.pkl"), "wb") as f:
             cloudpickle.dump(arts, f)

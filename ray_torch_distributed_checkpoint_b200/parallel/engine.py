@@ -1,0 +1,298 @@
+"""Whole-step engine for the reference MLP: forward, loss, backward, bucketed NVLink all-reduce and
+the optimizer as ONE replayable CUDA graph of hand-written kernels.
+
+The reference's hot loop (``/root/reference/my_ray_module.py:153-160``) launches ~30 library kernels per
+step and two NCCL all-reduces; here a step is (see ``_enqueue_train_step``):
+
+    u8->fp32 normalise · 3 fused forward GEMMs (bias+ReLU+dropout epilogues) · fused softmax-CE fwd+bwd ·
+    wgrad3 + colsum · dgrad3 (mask epilogue) · wgrad2 + colsum · [bucket0 all-reduce on the comm stream] ·
+    dgrad2 · wgrad1 + colsum · [bucket1 all-reduce] · fused SGD over the flat arena · counter advance
+
+Weight gradients are written by the wgrad kernels straight into the gradient arena, laid out exactly
+like torch DDP's buckets for this model (``buckets.plan``); with more than one rank that arena is
+peer-mapped symmetric memory and each bucket is reduced (x 1/world fused) as soon as its last gradient
+exists, overlapping the rest of backward. Parameters, gradients and momentum are three flat fp32
+arenas, so the optimizer is one kernel and a checkpoint snapshot is two contiguous copies.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .. import ops
+from ..models.mlp import NeuralNetwork
+from . import buckets as _buckets
+
+_LOGIT_LD = 16          # logits / dlogits rows padded to 16 floats (TMA needs 16-byte row pitch)
+
+
+class MLPTrainEngine:
+    def __init__(self, model: Optional[NeuralNetwork] = None, *, batch_size: int, lr: float = 1e-3, momentum: float = 0.9,
+                 weight_decay: float = 0.0, device=None, seed: int = 0x5EED, precision: int = ops.PRECISION_FP32,
+                 use_graph: bool = True, process_group=None, distributed: Optional[bool] = None, algo: str = "auto",
+                 input_mean: float = 0.5, input_std: float = 0.5):
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        if self.device.type == "cuda" and self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        if self.device.type != "cuda":
+            raise ValueError("MLPTrainEngine runs the sm_100a kernels and needs a CUDA device; CPU workers use the "
+                             "module path (prepare_model + optim.SGD)")
+        torch.cuda.set_device(self.device)
+        model = model if model is not None else NeuralNetwork()
+        lin = [m for m in model.linear_relu_stack if isinstance(m, torch.nn.Linear) or hasattr(m, "weight")]
+        if len(lin) != 3:
+            raise ValueError("MLPTrainEngine expects the reference's three-layer linear_relu_stack")
+        drops = [m.p for m in model.linear_relu_stack if isinstance(m, torch.nn.Dropout)]
+        fused_p = [getattr(m, "p_drop", 0.0) for m in model.linear_relu_stack if hasattr(m, "p_drop")]
+        self.p_drop = float(drops[0]) if drops else (float(max(fused_p)) if fused_p else 0.0)
+        self.B = int(batch_size)
+        self.d_in, self.d_h, self.d_out = lin[0].weight.shape[1], lin[0].weight.shape[0], lin[2].weight.shape[0]
+        if self.d_out > _LOGIT_LD:
+            raise ValueError(f"at most {_LOGIT_LD} classes")
+        self.seed, self.precision = seed, precision
+        self.mean, self.std = input_mean, input_std
+        self.world = dist.get_world_size(process_group) if (dist.is_initialized() and distributed is not False) else 1
+        self.rank = dist.get_rank(process_group) if self.world > 1 else 0
+        self.group = process_group
+        self.algo = algo
+
+        # ---- arenas (bucket order == torch DDP's for this model)
+        named = [(n, p) for n, p in model.named_parameters()]
+        self.buckets, total = _buckets.plan(named)
+        self.total = total
+        dev = self.device
+        self.p_arena = torch.zeros(total, device=dev)
+        self.m_arena = torch.zeros(total, device=dev)
+        self.symm = None
+        if self.world > 1:
+            from .symm import SymmetricArena
+            self.symm = SymmetricArena(total * 4 + 4096, device=dev, group=process_group)
+            self.g_off, self.g_arena = self.symm.alloc(total, torch.float32)
+            self.comm_stream = torch.cuda.Stream(dev)
+        else:
+            self.g_off, self.g_arena = 0, torch.zeros(total, device=dev)
+            self.comm_stream = None
+        self.slots: Dict[str, _buckets.ParamSlot] = {s.name: s for b in self.buckets for s in b.slots}
+        self.param_names = [n for n, _ in named]            # registration order (state_dict / optimizer order)
+        by_name = dict(named)
+        with torch.no_grad():
+            for name, s in self.slots.items():
+                self._view(self.p_arena, name).copy_(by_name[name].detach().to(dev, torch.float32))
+        if self.world > 1:
+            self._broadcast_params()
+        pre = "linear_relu_stack."
+        self.W = [self._view(self.p_arena, f"{pre}{i}.weight") for i in (0, 3, 6)]
+        self.b = [self._view(self.p_arena, f"{pre}{i}.bias") for i in (0, 3, 6)]
+        self.dW = [self._view(self.g_arena, f"{pre}{i}.weight") for i in (0, 3, 6)]
+        self.db = [self._view(self.g_arena, f"{pre}{i}.bias") for i in (0, 3, 6)]
+        self.bucket_of_layer = [self.slots[f"{pre}{i}.weight"].bucket for i in (0, 3, 6)]
+
+        # ---- static activations (graph replays need fixed addresses)
+        B = self.B
+        self.x_u8 = torch.zeros(B, self.d_in, dtype=torch.uint8, device=dev)
+        self.x = torch.zeros(B, self.d_in, device=dev)
+        self.y = torch.zeros(B, dtype=torch.int64, device=dev)
+        self.h1 = torch.empty(B, self.d_h, device=dev)
+        self.h2 = torch.empty(B, self.d_h, device=dev)
+        self.z = torch.zeros(B, _LOGIT_LD, device=dev)
+        self.dz = torch.zeros(B, _LOGIT_LD, device=dev)
+        self.dh2 = torch.empty(B, self.d_h, device=dev)
+        self.dh1 = torch.empty(B, self.d_h, device=dev)
+        self.loss = torch.zeros((), device=dev)
+        self.step_counter = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.eval_loss_sum = torch.zeros((), device=dev)
+        self.eval_correct = torch.zeros((), dtype=torch.int64, device=dev)
+        self.sgd = ops.SgdState(dev, lr, momentum, 0.0, weight_decay, False)
+        self.lr, self.momentum, self.weight_decay = lr, momentum, weight_decay
+        self.steps_done = 0
+        self.use_graph = use_graph
+        self._graphs: Dict[str, torch.cuda.CUDAGraph] = {}
+        self._warm: Dict[str, int] = {}
+        self.stream = torch.cuda.Stream(dev)
+        self.kernel_launches_per_step = {}
+
+    # ------------------------------------------------------------------------------------------ helpers
+    def _view(self, arena: torch.Tensor, name: str) -> torch.Tensor:
+        s = self.slots[name]
+        return arena[s.offset:s.offset + s.numel].view(s.shape)
+
+    def _broadcast_params(self):
+        """C2: every replica starts from rank 0's parameters, pulled over NVLink through the symmetric arena."""
+        stage = self.symm.tensor(self.g_off, self.total, torch.float32)
+        if self.rank == 0:
+            stage.copy_(self.p_arena)
+        torch.cuda.current_stream().synchronize()
+        self.symm.broadcast(self.g_off, self.total * 4, 0, self.p_arena)
+        torch.cuda.current_stream().synchronize()
+        stage.zero_()
+
+    def _reduce_bucket(self, b: int, main: torch.cuda.Stream):
+        if self.world == 1:
+            return
+        bk = self.buckets[b]
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self.comm_stream.wait_event(ev)
+        self.symm.all_reduce(self.g_off + bk.offset * 4, bk.numel, scale=1.0 / self.world, algo=self.algo,
+                             stream=self.comm_stream)
+
+    # ------------------------------------------------------------------------------------------ the step
+    def _forward(self, s, train: bool, from_u8: bool):
+        n = 0
+        p = self.p_drop if train else 0.0
+        kw = dict(seed=self.seed, step_tensor=self.step_counter, precision=self.precision, stream=s)
+        if from_u8:
+            ops.u8_normalize(self.x_u8, mean=self.mean, std=self.std, out=self.x, stream=s); n += 1
+        ops.linear_forward(self.x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, **kw); n += 1
+        ops.linear_forward(self.h1, self.W[1], self.b[1], relu=True, drop_p=p, salt=2, out=self.h2, **kw); n += 1
+        ops.linear_forward(self.h2, self.W[2], self.b[2], relu=True, out=self.z, n_store=_LOGIT_LD, **kw); n += 1
+        return n
+
+    def _enqueue_train_step(self, s: torch.cuda.Stream, from_u8: bool) -> int:
+        B, prec = self.B, self.precision
+        inv_keep = 1.0 / (1.0 - self.p_drop) if self.p_drop > 0 else 1.0
+        n = self._forward(s, True, from_u8)
+        ops.softmax_cross_entropy(self.z, self.y, classes=self.d_out, dlogits=self.dz, grad_scale=1.0 / B, relu_mask=True,
+                                  loss_out=self.loss, stream=s); n += 1
+        # layer 3
+        ops.linear_wgrad(self.dz, self.h2, N_out=self.d_out, out=self.dW[2], precision=prec, stream=s); n += 2
+        ops.colsum(self.dz, cols=self.d_out, out=self.db[2], stream=s); n += 1
+        ops.linear_dgrad(self.dz, self.W[2], N_out=self.d_out, mask_src=self.h2, mask_scale=inv_keep, out=self.dh2,
+                         precision=prec, stream=s); n += 1
+        # layer 2
+        ops.linear_wgrad(self.dh2, self.h1, out=self.dW[1], precision=prec, stream=s); n += 2
+        ops.colsum(self.dh2, out=self.db[1], stream=s); n += 1
+        launched = set()
+        if self.bucket_of_layer[1] != self.bucket_of_layer[0]:
+            self._reduce_bucket(self.bucket_of_layer[1], s); launched.add(self.bucket_of_layer[1]); n += self.world > 1
+        ops.linear_dgrad(self.dh2, self.W[1], mask_src=self.h1, mask_scale=inv_keep, out=self.dh1, precision=prec, stream=s); n += 1
+        # layer 1 (its input needs no gradient)
+        ops.linear_wgrad(self.dh1, self.x, out=self.dW[0], precision=prec, stream=s); n += 2
+        ops.colsum(self.dh1, out=self.db[0], stream=s); n += 1
+        for b in range(len(self.buckets)):
+            if b not in launched:
+                self._reduce_bucket(b, s); n += self.world > 1
+        if self.world > 1:
+            s.wait_stream(self.comm_stream)
+        ops.sgd_step(self.p_arena, self.g_arena, self.m_arena, self.sgd, stream=s); n += 1
+        ops.counter_advance(self.step_counter, self.sgd, stream=s); n += 1
+        return n
+
+    def _enqueue_eval(self, s: torch.cuda.Stream, from_u8: bool) -> int:
+        n = self._forward(s, False, from_u8)
+        ops.softmax_cross_entropy(self.z, self.y, classes=self.d_out, loss_out=self.loss, loss_sum_accum=self.eval_loss_sum,
+                                  correct_accum=self.eval_correct, stream=s)
+        return n + 1
+
+    def _run(self, key: str, enqueue):
+        """Two eager warm-up executions (allocations, scratch, first-step flag), then capture + replay."""
+        s = self.stream
+        s.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(s):
+            if not self.use_graph or self._warm.get(key, 0) < 2:
+                self.kernel_launches_per_step[key] = enqueue(s)
+                self._warm[key] = self._warm.get(key, 0) + 1
+            else:
+                g = self._graphs.get(key)
+                if g is None:
+                    if self.world > 1:
+                        dist.barrier(group=self.group)      # all ranks capture (and first replay) together
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
+                        self.kernel_launches_per_step[key] = enqueue(s)
+                    self._graphs[key] = g
+                g.replay()
+        torch.cuda.current_stream(self.device).wait_stream(s)
+
+    def _load_inputs(self, x: torch.Tensor, y: torch.Tensor) -> bool:
+        """Copy a batch into the static input buffers (H2D when ``x``/``y`` live in pinned host memory,
+        D2D otherwise). Returns True when ``x`` is uint8 pixels that still need normalising."""
+        if x.shape[0] != self.B:
+            raise ValueError(f"engine was built for batches of {self.B} samples (got {x.shape[0]})")
+        x2 = x.reshape(self.B, -1)
+        self.y.copy_(y, non_blocking=True)
+        if x2.dtype == torch.uint8:
+            self.x_u8.copy_(x2, non_blocking=True)
+            return True
+        self.x.copy_(x2, non_blocking=True)
+        return False
+
+    # ------------------------------------------------------------------------------------------ public API
+    def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """One optimizer step on a batch (uint8 pixels or normalised float32). Returns the device-resident
+        mean loss of this rank's batch (``.item()`` to read it back)."""
+        from_u8 = self._load_inputs(x, y)
+        self._run("train_u8" if from_u8 else "train_f32", lambda s: self._enqueue_train_step(s, from_u8))
+        self.steps_done += 1
+        return self.loss
+
+    def eval_batch(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """Forward + loss on a batch, accumulating ``eval_loss_sum`` / ``eval_correct`` on the device."""
+        from_u8 = self._load_inputs(x, y)
+        self._run("eval_u8" if from_u8 else "eval_f32", lambda s: self._enqueue_eval(s, from_u8))
+        return self.loss
+
+    def reset_eval(self):
+        self.eval_loss_sum.zero_()
+        self.eval_correct.zero_()
+
+    def read_eval(self):
+        """(sum of per-batch mean losses, correct predictions): one D2H per call (ref: two per batch)."""
+        return float(self.eval_loss_sum.item()), int(self.eval_correct.item())
+
+    def predict(self, x: torch.Tensor) -> torch.Tensor:
+        """Logits ``[B, classes]`` for a batch (eval mode)."""
+        from_u8 = self._load_inputs(x, torch.zeros(self.B, dtype=torch.int64, device=self.device))
+        s = torch.cuda.current_stream(self.device)
+        self._forward(s, False, from_u8)
+        return self.z[:, :self.d_out].clone()
+
+    def set_lr(self, lr: float):
+        self.lr = lr
+        self.sgd.update(lr=lr)
+
+    # ---- state in the reference's checkpoint format ------------------------------------------------
+    def model_state_dict(self, prefix: Optional[str] = None) -> Dict[str, torch.Tensor]:
+        """Views into the parameter arena, keyed like ``NeuralNetwork.state_dict()``; with more than one
+        rank the keys carry DDP's ``module.`` prefix (ref my_ray_module.py:182,261)."""
+        pre = ("module." if self.world > 1 else "") if prefix is None else prefix
+        return {pre + n: self._view(self.p_arena, n) for n in self.param_names}
+
+    def optimizer_state_dict(self) -> Dict[str, Any]:
+        state = {}
+        if self.momentum != 0 and self.steps_done > 0:
+            state = {i: {"momentum_buffer": self._view(self.m_arena, n)} for i, n in enumerate(self.param_names)}
+        return {"state": state,
+                "param_groups": [dict(lr=self.lr, momentum=self.momentum, dampening=0, weight_decay=self.weight_decay,
+                                      nesterov=False, maximize=False, foreach=None, differentiable=False, fused=None,
+                                      params=list(range(len(self.param_names))))]}
+
+    def load_model_state_dict(self, sd: Dict[str, torch.Tensor]):
+        with torch.no_grad():
+            for k, v in sd.items():
+                name = k[len("module."):] if k.startswith("module.") else k
+                self._view(self.p_arena, name).copy_(v)
+
+    def load_optimizer_state_dict(self, sd: Dict[str, Any]):
+        g = sd["param_groups"][0]
+        self.lr, self.momentum, self.weight_decay = g["lr"], g["momentum"], g["weight_decay"]
+        with torch.no_grad():
+            for i, st in sd["state"].items():
+                self._view(self.m_arena, self.param_names[int(i)]).copy_(st["momentum_buffer"])
+        resumed = bool(sd["state"])
+        self.sgd.update(lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay, first_step=0 if resumed else 1)
+        if resumed:
+            self.steps_done = max(self.steps_done, 1)
+
+    def copy_to_module(self, model: torch.nn.Module):
+        model.load_state_dict({k: v.detach().clone() for k, v in self.model_state_dict(prefix="").items()})
+        return model
+
+    def close(self):
+        self._graphs.clear()
+        if self.symm is not None:
+            torch.cuda.synchronize(self.device)
+            self.symm.close()
+            self.symm = None

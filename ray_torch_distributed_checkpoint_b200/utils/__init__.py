@@ -1,0 +1,5 @@
+"""Timing, tracing and GPU sampling helpers: CUDA-event step timers with max-over-ranks,
+NVTX ranges, an NVML sampler (the ``@gpu_profile`` equivalent)."""
+from .profiling import GpuSampler, StepTimer, max_over_ranks, nvtx_range
+
+__all__ = ["GpuSampler", "StepTimer", "max_over_ranks", "nvtx_range"]

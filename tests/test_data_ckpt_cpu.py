@@ -94,11 +94,15 @@ def test_synthetic_fashion_mnist_and_idx_writer(tmp_path):
 
 def test_u8_loader_cpu_path():
     ds = data.FashionMNISTSynthetic(train=True, size=100, raw=True)
-    loader = data.U8BatchLoader(ds.data, ds.targets, 32, "cpu", shuffle=False)
+    loader = data.U8BatchLoader(ds.data, ds.targets, 32, "cpu", shuffle=False, normalize=True)
     batches = list(loader)
     assert len(batches) == 3 and batches[0][0].shape == (32, 784) and batches[0][0].dtype == torch.float32
     assert torch.allclose(batches[0][0], ds.normalized()[:32].reshape(32, -1))
     assert torch.equal(batches[1][1], ds.targets[32:64])
+    raw = list(data.U8BatchLoader(ds.data, ds.targets, 32, "cpu", shuffle=True, world=2, rank=1, seed=3))
+    assert len(raw) == 1 and raw[0][0].dtype == torch.uint8 and raw[0][0].shape == (32, 784)
+    ref = data.DistributedSampler(100, 2, 1, shuffle=True, seed=3).indices()[:32]
+    assert torch.equal(raw[0][1], ds.targets[ref]) and torch.equal(raw[0][0], ds.data.reshape(100, -1)[ref])
 
 
 def _ref_state():
