@@ -1,0 +1,111 @@
+"""North-star model configurations under data parallelism: ResNet-50 (bf16, 224x224 synthetic) and
+GPT-2 small (bf16, 1024-token synthetic), comparing this framework's DDP (flat symmetric-memory
+arenas + NVLink all-reduce kernels overlapped with backward) with stock torch DDP + NCCL on the same
+GPUs. Launch: python -m torch.distributed.run --nproc-per-node N tools/bench_models.py --model gpt2 --ddp ours
+Prints one JSON line from rank 0; device-timed with CUDA events, max over ranks."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from ray_torch_distributed_checkpoint_b200.models import GPT2, GPT2Config, resnet50  # noqa: E402
+from ray_torch_distributed_checkpoint_b200.parallel.ddp import DistributedDataParallel  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", choices=["resnet50", "gpt2"], required=True)
+    ap.add_argument("--ddp", choices=["ours", "torch"], default="ours")
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--algo", default="auto")
+    ap.add_argument("--ckpt-every", type=int, default=0, help="async checkpoint every N steps (ours) / torch.save (torch)")
+    args = ap.parse_args()
+    rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    torch.manual_seed(0)
+    torch.backends.cudnn.benchmark = True
+    if args.model == "resnet50":
+        B = args.batch or 128
+        model = resnet50().to(dev, dtype=torch.bfloat16, memory_format=torch.channels_last)
+        x = torch.randn(B, 3, 224, 224, device=dev, dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        y = torch.randint(0, 1000, (B,), device=dev)
+        loss_of = lambda m: torch.nn.functional.cross_entropy(m(x).float(), y)
+        opt_cls = lambda p: torch.optim.SGD(p, lr=0.1, momentum=0.9)
+        per_sample = 1
+    else:
+        B = args.batch or 16
+        model = GPT2(GPT2Config()).to(dev, dtype=torch.bfloat16)
+        idx = torch.randint(0, 50257, (B, 1024), device=dev)
+        tgt = torch.randint(0, 50257, (B, 1024), device=dev)
+        loss_of = lambda m: m(idx, tgt)
+        opt_cls = lambda p: torch.optim.AdamW(p, lr=3e-4, fused=True)
+        per_sample = 1024
+    if world > 1:
+        if args.ddp == "ours":
+            model = DistributedDataParallel(model, device=dev, algo=args.algo)
+        else:
+            model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True)
+    opt = opt_cls(model.parameters())
+    ckpt = None
+    if args.ckpt_every and rank == 0 and args.ddp == "ours":
+        from ray_torch_distributed_checkpoint_b200.ckpt import AsyncCheckpointer
+        ckpt = AsyncCheckpointer(dev)
+    ckpt_dir = os.path.join("/tmp", f"rtdc_bench_ckpt_{os.getpid()}")
+
+    def step(i):
+        if isinstance(model, DistributedDataParallel):
+            model.zero_grad()
+        else:
+            opt.zero_grad(set_to_none=False)
+        loss = loss_of(model)
+        loss.backward()
+        opt.step()
+        if args.ckpt_every and rank == 0 and (i + 1) % args.ckpt_every == 0:
+            state = {"step": i, "model_state_dict": model.state_dict(), "optimizer_state_dict": opt.state_dict()}
+            if ckpt is not None:
+                ckpt.save(state, ckpt_dir, "latest_model.pt")
+            else:
+                os.makedirs(ckpt_dir, exist_ok=True)
+                torch.save(state, os.path.join(ckpt_dir, "latest_model.pt"))
+        return loss
+
+    for i in range(args.warmup):
+        step(i)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        loss = step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    if ckpt is not None:
+        ckpt.wait()
+    if rank == 0:
+        print(json.dumps({"model": args.model, "ddp": args.ddp, "n_gpus": world, "batch_per_gpu": B, "steps": args.steps,
+                          "ms_per_step": round(ms / args.steps, 3), "samples_per_s": round(B * world * args.steps / (ms / 1e3), 1),
+                          "tokens_per_s": round(B * world * per_sample * args.steps / (ms / 1e3), 1) if per_sample > 1 else None,
+                          "ckpt_every": args.ckpt_every, "loss": round(float(loss), 4), "dtype": "bf16"}), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
