@@ -87,6 +87,26 @@ size_t rtdc_colsum_scratch_bytes(int rows, int cols);
 int rtdc_colsum(const float* x, int ld, int rows, int cols, float* out, void* scratch, size_t scratch_bytes,
                 void* stream);
 
+/* Column sums without any device allocation, for callers that cannot call cudaMalloc (a server whose
+ * memory arena already owns all free HBM, a latency-critical loop that must avoid the device-wide
+ * synchronisation of cudaMalloc/cudaFree, an embedder without a caching allocator). Same result as
+ * rtdc_colsum, but the scratch (partial sums + arrival counters) is a fixed array inside the library
+ * image: RTDC_COLSUM_NOALLOC_SCRATCH_BYTES of device memory on every GPU that loads the library, held
+ * until the process exits.
+ *   - cols must be <= RTDC_COLSUM_NOALLOC_MAX_COLS; wider inputs are rejected with an error message
+ *     (use rtdc_colsum with your own scratch for those). rows is unlimited.
+ *   - The first call on each device looks the array's address up (cudaGetSymbolAddress, with that
+ *     device current) and remembers it; make that first call before starting any stream capture.
+ *   - No cudaMalloc / cudaFree / allocating library routine is called, on the first call or later.
+ *   - All calls on a device share the one array. Each call clears the counters it depends on before
+ *     launching, so a call never inherits state from the previous one; but two calls that can run on
+ *     the GPU at the same time (different streams without an ordering between them) race on it and
+ *     give wrong sums. Order them on one stream or with events.
+ * This entry point has no counterpart in the reference (which ships no native code). */
+#define RTDC_COLSUM_NOALLOC_MAX_COLS 1024
+#define RTDC_COLSUM_NOALLOC_SCRATCH_BYTES (4096 + 64 * (RTDC_COLSUM_NOALLOC_MAX_COLS / 128) * 128 * 4)
+int rtdc_colsum_noalloc(const float* x, int ld, int rows, int cols, float* out, void* stream);
+
 /* uint8 pixels -> normalised fp32 ((x/255 - mean)/std; ref: my_ray_module.py:38 ToTensor+Normalize). */
 int rtdc_u8_normalize(const uint8_t* src, float* dst, size_t n, float mean, float std, void* stream);
 

@@ -367,6 +367,66 @@ RTDC_API int rtdc_colsum(const float* x, int ld, int rows, int cols, float* out,
   return RTDC_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Column sums for callers that must not allocate device memory.
+//
+// Who this is for: hosts that handed out all of their device memory up front and keep it that way —
+// an inference server whose arena already owns every free byte of HBM (a cudaMalloc there simply
+// fails), a real-time loop that cannot afford the device-wide synchronisation cudaMalloc/cudaFree
+// imply, or a plain C/C++ embedder that has no caching allocator to borrow a workspace from. The
+// regular rtdc_colsum makes such a caller find `rtdc_colsum_scratch_bytes` of zeroed device memory;
+// this variant brings its own: the partial sums and arrival counters live in a file-scope __device__
+// array that is part of the library image (each GPU that loads the library carries it until exit).
+constexpr int COLSUM_NOALLOC_MAX_COLS = RTDC_COLSUM_NOALLOC_MAX_COLS;
+constexpr size_t COLSUM_NOALLOC_SCRATCH_BYTES =
+    CS_COUNTER_BYTES + static_cast<size_t>(CS_MAX_SLABS) * (COLSUM_NOALLOC_MAX_COLS / CS_COLS) * CS_COLS * sizeof(float);
+static_assert(COLSUM_NOALLOC_SCRATCH_BYTES == RTDC_COLSUM_NOALLOC_SCRATCH_BYTES, "header and kernel disagree on the built-in scratch size");
+static __device__ __align__(256) unsigned char g_colsum_noalloc_scratch[COLSUM_NOALLOC_SCRATCH_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static void* g_colsum_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+// In host code `g_colsum_noalloc_scratch` is only a handle for the symbol, not a device address; the
+// address has to be asked for, once per device, with that device current.
+static int colsum_noalloc_scratch(void** out) {
+  int dev = -1;
+  RTDC_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return rtdc::fail(rtdc::RTDC_ERR_LIMIT, "colsum_noalloc: device ordinal %d not supported (max %d)", dev, NOALLOC_MAX_DEVICES - 1);
+  void* p = __atomic_load_n(&g_colsum_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    RTDC_CUDA_CHECK(cudaGetSymbolAddress(&p, g_colsum_noalloc_scratch));
+    if (p == nullptr) return rtdc::fail(rtdc::RTDC_ERR_CUDA, "colsum_noalloc: cudaGetSymbolAddress returned a null address");
+    __atomic_store_n(&g_colsum_noalloc_ptr[dev], p, __ATOMIC_RELEASE);  // racing first calls resolve the same address
+  }
+  *out = p;
+  return rtdc::RTDC_OK;
+}
+
+RTDC_API int rtdc_colsum_noalloc(const float* x, int ld, int rows, int cols, float* out, void* stream) {
+  if (!x || !out || rows <= 0 || cols <= 0 || ld < cols) return fail(RTDC_ERR_ARG, "colsum_noalloc: bad arguments");
+  if (cols > COLSUM_NOALLOC_MAX_COLS)
+    return fail(RTDC_ERR_LIMIT, "colsum_noalloc: %d columns exceed the built-in scratch (at most %d columns; use rtdc_colsum with "
+                "caller-provided scratch for wider matrices)", cols, COLSUM_NOALLOC_MAX_COLS);
+  int cg, slabs, rps;
+  colsum_shape(rows, cols, &cg, &slabs, &rps);
+  const size_t need = CS_COUNTER_BYTES + static_cast<size_t>(slabs) * cg * CS_COLS * sizeof(float);
+  if (need > COLSUM_NOALLOC_SCRATCH_BYTES)
+    return fail(RTDC_ERR_LIMIT, "colsum_noalloc: needs %zu bytes of scratch, built-in scratch holds %zu", need, COLSUM_NOALLOC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  int rc = colsum_noalloc_scratch(&scratch);
+  if (rc != RTDC_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // The array is shared by every call and still holds what the previous one left. The kernel only needs
+  // its arrival counters to start at zero (it overwrites the partial sums before reading them); clear
+  // them here rather than trusting that the last call ran to completion.
+  RTDC_CUDA_CHECK(cudaMemsetAsync(scratch, 0, CS_COUNTER_BYTES, st));
+  unsigned int* counters = static_cast<unsigned int*>(scratch);
+  float* partial = reinterpret_cast<float*>(static_cast<unsigned char*>(scratch) + CS_COUNTER_BYTES);
+  colsum_kernel<<<dim3(cg, slabs), CS_THREADS, 0, st>>>(x, ld, rows, cols, out, partial, counters, rps);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
 RTDC_API int rtdc_u8_normalize(const uint8_t* src, float* dst, size_t n, float mean, float std, void* stream) {
   if (!src || !dst) return fail(RTDC_ERR_ARG, "u8_normalize: null pointer");
   if (n == 0) return RTDC_OK;
