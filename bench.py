@@ -160,7 +160,8 @@ def run_ours(args):
     n_host = B * (K + max(W, 3))
     hx = torch.randint(0, 256, (n_host, 784), dtype=torch.uint8, generator=g)
     hy = torch.randint(0, 10, (n_host,), generator=g)
-    loader = data.U8BatchLoader(hx, hy, B, dev, shuffle=True, seed=5, lookahead=args.lookahead)
+    loader = data.U8BatchLoader(hx, hy, B, dev, shuffle=True, seed=5, lookahead=args.lookahead,
+                                prefetch_next_epoch=False)   # one epoch only: no background shuffle of a next one
     loss_host = torch.zeros(4, dtype=torch.float32).pin_memory()
     it = iter(loader)
     for _ in range(max(W, 3)):
@@ -325,7 +326,8 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--batch-per-gpu", type=int, default=int(os.environ.get("RTDC_BENCH_BATCH", 16384)))
+    ap.add_argument("--batch-per-gpu", type=int, default=int(os.environ.get("RTDC_BENCH_BATCH", 18944)),
+                    help="per-GPU batch; 18944 = 148 SMs x 128 rows, i.e. exactly two waves of 128x256 output tiles")
     ap.add_argument("--rotate", type=int, default=4, help="distinct device-resident input batches for the device-timed loop")
     ap.add_argument("--lookahead", type=int, default=2, help="H2D batches in flight ahead of the consumer (e2e loop)")
     ap.add_argument("--algo", default="auto", choices=["auto", "two_shot", "nvls"])

@@ -52,9 +52,9 @@ __device__ __forceinline__ void group_barrier(const SymmView& sv, unsigned int s
     st_release_sys(theirs, seq);
     const unsigned int* mine = static_cast<const unsigned int*>(sv.pads[sv.rank]) + blockIdx.x * RTDC_SYMM_MAX_WORLD + peer;
     if (static_cast<int>(ld_acquire_sys(mine) - seq) < 0) {
-      const uint64_t t0 = global_timer_ns();
+      const long long t0 = clock64();
       while (static_cast<int>(ld_acquire_sys(mine) - seq) < 0) {
-        if (global_timer_ns() - t0 > RTDC_WAIT_TIMEOUT_NS * 4) {
+        if (clock64() - t0 > RTDC_WAIT_TIMEOUT_CYCLES * 4) {
           printf("rtdc: rank %d block %d timed out waiting for rank %d (seq %u)\n", sv.rank, blockIdx.x, peer, seq);
           __trap();
         }

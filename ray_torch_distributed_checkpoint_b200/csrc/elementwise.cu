@@ -146,7 +146,20 @@ colsum_kernel(const float* __restrict__ x, int ld, int rows, int cols, float* __
   const int r_begin = slab * rows_per_slab, r_end = min(rows, r_begin + rows_per_slab);
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   const bool vec = ((ld & 3) == 0) && (c0 + 3 < cols) && ((reinterpret_cast<uintptr_t>(x) & 15u) == 0);
-  for (int r = r_begin + warp; r < r_end; r += CS_THREADS / 32) {
+  constexpr int ROWS_ILP = 8;   // independent row loads in flight per thread (the loop is latency bound otherwise)
+  constexpr int WARPS = CS_THREADS / 32;
+  int r = r_begin + warp;
+  if (vec) {
+    for (; r + (ROWS_ILP - 1) * WARPS < r_end; r += ROWS_ILP * WARPS) {
+      float4 t[ROWS_ILP];
+#pragma unroll
+      for (int u = 0; u < ROWS_ILP; ++u)
+        t[u] = __ldg(reinterpret_cast<const float4*>(x + static_cast<size_t>(r + u * WARPS) * ld + c0));
+#pragma unroll
+      for (int u = 0; u < ROWS_ILP; ++u) { acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w; }
+    }
+  }
+  for (; r < r_end; r += WARPS) {
     const float* src = x + static_cast<size_t>(r) * ld + c0;
     if (vec) {
       const float4 t = __ldg(reinterpret_cast<const float4*>(src));

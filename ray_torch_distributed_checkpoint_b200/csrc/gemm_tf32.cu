@@ -30,9 +30,11 @@ constexpr int BM = 128;           // tile rows == TMEM lanes
 constexpr int UMMA_K = 8;         // tf32: 32 bytes per instruction along K
 constexpr int MAX_STAGES = 4;
 constexpr int MAX_BN = 256;
-constexpr int TMEM_COLS = 256;
-constexpr int NUM_THREADS = 192;  // 6 warps
-constexpr int EPI_THREADS = 128;  // warps 2..5
+constexpr int TMEM_COLS = 512;      // two 256-column accumulator buffers (epilogue of one tile overlaps the next main loop)
+constexpr int NUM_THREADS = 320;    // 10 warps: 0 TMA producer, 1 MMA issuer, 2-5 splitters, 6-9 epilogue
+constexpr int SPLIT_THREADS = 128;
+constexpr int EPI_THREADS = 128;
+constexpr int EPI_STAGING_BYTES = 32768;  // 4 epilogue warps x two 32x32 fp32 TMA-store boxes
 constexpr int SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
 constexpr int STATIC_SMEM_RESERVE = 2048;  // barriers, bias slice, flags (static __shared__)
 
@@ -46,7 +48,7 @@ struct GemmParams {
   float drop_scale; uint32_t drop_thr16; uint32_t seed_lo, seed_hi; const uint32_t* step_ptr; uint32_t step_imm, salt;
   const float* mask_src; int ldm; float mask_scale;
   float* scratch;
-  int debug;  // timing experiments only (RTDC_GEMM_DEBUG): 1 = no TMA loads, 2 = no MMAs, 4 = no global stores
+  int debug;  // timing experiments only (RTDC_GEMM_DEBUG): 1 = no TMA loads, 2 = no MMAs, 4 = no global stores, 8 = no split pass, 16 = no proxy fence
   int tma_store;         // epilogue goes through smem + cp.async.bulk.tensor stores (tmOut valid)
   long long* dbg_times;  // RTDC_GEMM_DEBUG_BUF: per-CTA clock64 stamps [grid][8]
 };
@@ -65,39 +67,30 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t ready_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
-  __shared__ __align__(8) uint64_t accum_bar;
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];    // MMA -> epilogue: accumulator buffer complete
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];   // epilogue -> MMA: accumulator buffer drained
   __shared__ uint32_t tmem_base_slot;
   __shared__ float s_bias[MAX_BN];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // 1024-byte aligned stage ring (128B swizzle atoms are 1024 B)
+  // 1024-byte aligned stage ring (swizzle atoms are up to 1024 B), epilogue staging right behind it
   const uint32_t dyn_base = smem_u32(smem_dyn);
   const uint32_t ring = (dyn_base + 1023u) & ~1023u;
   uint8_t* ring_ptr = smem_dyn + (ring - dyn_base);
-
-  const int tile = blockIdx.x;
-  const int m_tile = tile % p.m_tiles;
-  const int n_tile = tile / p.m_tiles;
-  const int m0 = m_tile * BM;
-  const int n0 = n_tile * p.bn;
-  const int split = blockIdx.y;
-  const int kb_begin = split * p.kb_per_split;
-  const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
-  const int n_iters = kb_end - kb_begin;
-
-  // columns this tile really owns, and the (multiple of 16) N the MMA runs at
-  const int n_valid = min(p.bn, p.N - n0);
-  const uint32_t umma_n = static_cast<uint32_t>(min(p.bn, (n_valid + 15) & ~15));
+  uint8_t* staging = ring_ptr + static_cast<size_t>(p.stages) * p.stage_bytes;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&ready_bar[s], EPI_THREADS / 32);
+      mbar_init(&ready_bar[s], SPLIT_THREADS / 32);
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(&accum_bar, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full_bar[b], 1);
+      mbar_init(&tmem_empty_bar[b], EPI_THREADS / 32);
+    }
     mbar_fence_init();
   }
   if (warp == 0 && lane == 0) {
@@ -113,31 +106,47 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
-  long long* stamps = p.dbg_times ? p.dbg_times + (static_cast<size_t>(blockIdx.y) * gridDim.x + blockIdx.x) * 8 : nullptr;
+  long long* stamps = p.dbg_times ? p.dbg_times + static_cast<size_t>(blockIdx.x) * 8 : nullptr;
   if (stamps && threadIdx.x == 0) { stamps[0] = clock64(); stamps[7] = static_cast<long long>(global_timer_ns()); }
+
+  // A CTA walks over work units (output tile x K split) round-robin; every role derives the same
+  // sequence, so the smem ring and the two TMEM accumulator buffers just keep cycling across units and
+  // the epilogue of unit j overlaps the main loop of unit j+1.
+  const int tiles = p.m_tiles * p.n_tiles;
+  const int total_units = tiles * p.splits;
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      for (int it = 0; it < n_iters; ++it) {
-        const int s = it % p.stages;
-        const uint32_t ph = (it / p.stages) & 1;
-        mbar_wait(&empty_bar[s], ph ^ 1u);
-        uint8_t* sa = ring_ptr + static_cast<size_t>(s) * p.stage_bytes;
-        uint8_t* sb = sa + p.a_bytes;
-        if (p.debug & 1) { mbar_arrive(&full_bar[s]); continue; }
-        mbar_expect_tx(&full_bar[s], p.a_bytes + p.b_bytes);
-        const int k0 = (kb_begin + it) * BK;
-        if (!A_MN) {
-          tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
-        } else {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
+        const int tile = u % tiles, split = u / tiles;
+        const int m0 = (tile % p.m_tiles) * BM, n0 = (tile / p.m_tiles) * p.bn;
+        const int kb_begin = split * p.kb_per_split;
+        const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
+        for (int it = 0; it < n_iters; ++it) {
+          mbar_wait(&empty_bar[s], ph ^ 1u);
+          uint8_t* sa = ring_ptr + static_cast<size_t>(s) * p.stage_bytes;
+          uint8_t* sb = sa + p.a_bytes;
+          if (p.debug & 1) {
+            mbar_arrive(&full_bar[s]);
+          } else {
+            mbar_expect_tx(&full_bar[s], p.a_bytes + p.b_bytes);
+            const int k0 = (kb_begin + it) * BK;
+            if (!A_MN) {
+              tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
+            } else {
 #pragma unroll
-          for (int b = 0; b < BM / 32; ++b) tma_load_2d(sa + b * (128 * BK), &tmA, &full_bar[s], m0 + 32 * b, k0);
-        }
-        if (!B_MN) {
-          tma_load_2d(sb, &tmB, &full_bar[s], k0, n0);
-        } else {
-          for (int b = 0; b < p.bn / 32; ++b) tma_load_2d(sb + b * (128 * BK), &tmB, &full_bar[s], n0 + 32 * b, k0);
+              for (int b = 0; b < BM / 32; ++b) tma_load_2d(sa + b * (128 * BK), &tmA, &full_bar[s], m0 + 32 * b, k0);
+            }
+            if (!B_MN) {
+              tma_load_2d(sb, &tmB, &full_bar[s], k0, n0);
+            } else {
+              for (int b = 0; b < p.bn / 32; ++b) tma_load_2d(sb + b * (128 * BK), &tmB, &full_bar[s], n0 + 32 * b, k0);
+            }
+          }
+          if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
       }
     }
@@ -145,12 +154,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      const uint32_t idesc = umma_idesc(UMMA_TF32, A_MN, B_MN, umma_n);
       const uint32_t tail_off = p.a_bytes + p.b_bytes;  // tails live right after the raw tiles
-      // K-major: 8-row groups 1024 B apart (SW128). MN-major: 32-wide MN blocks 4096 B apart, 4-row
-      // K groups 512 B apart (SW128 with 32-byte atoms: the only MN-major layout tf32 accepts).
-      // With BK = 16 a K-major row is 64 B: 64-byte swizzle, 8-row groups 512 B apart; an MN-major box
-      // then holds 16 K rows (2048 B).
+      // K-major: 8-row groups (SW128 for 128-byte rows, SW64 for 64-byte rows). MN-major: 32-wide MN blocks
+      // one TMA box apart, 4-row K groups 512 B apart (SW128 with 32-byte atoms: the only MN-major layout
+      // tf32 accepts).
       constexpr uint32_t kmajor_sbo = 8u * BK * 4u;
       constexpr uint32_t kmajor_lt = BK == 32 ? UMMA_LAYOUT_SW128 : UMMA_LAYOUT_SW64;
       constexpr uint32_t mn_box = 128u * BK;
@@ -159,123 +166,176 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t a_lt = A_MN ? UMMA_LAYOUT_SW128_BASE32B : kmajor_lt;
       const uint32_t b_lt = B_MN ? UMMA_LAYOUT_SW128_BASE32B : kmajor_lt;
       const uint32_t a_kstep = A_MN ? 1024u : 32u, b_kstep = B_MN ? 1024u : 32u;
-      for (int it = 0; it < n_iters; ++it) {
-        const int s = it % p.stages;
-        const uint32_t ph = (it / p.stages) & 1;
-        mbar_wait(NSPLIT == 3 ? &ready_bar[s] : &full_bar[s], ph);
+      int s = 0;
+      uint32_t ph = 0;
+      int j = 0;
+      for (int u = blockIdx.x; u < total_units; u += gridDim.x, ++j) {
+        const int tile = u % tiles, split = u / tiles;
+        const int n0 = (tile / p.m_tiles) * p.bn;
+        const int kb_begin = split * p.kb_per_split;
+        const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
+        const int n_valid = min(p.bn, p.N - n0);
+        const uint32_t umma_n = static_cast<uint32_t>(min(p.bn, (n_valid + 15) & ~15));
+        const uint32_t idesc = umma_idesc(UMMA_TF32, A_MN, B_MN, umma_n);
+        const int buf = j & 1;
+        mbar_wait(&tmem_empty_bar[buf], ((j >> 1) & 1) ^ 1u);   // the epilogue has drained this buffer
         tcgen05_fence_after();
-        const uint32_t sa = ring + static_cast<uint32_t>(s) * p.stage_bytes;
-        const uint32_t sb = sa + p.a_bytes;
-        if (p.debug & 2) { mbar_arrive(&empty_bar[s]); continue; }
-        const int k_left = p.K - (kb_begin + it) * BK;
-        const int ksteps = min(BK / UMMA_K, (k_left + UMMA_K - 1) / UMMA_K);
-        for (int j = 0; j < ksteps; ++j) {
-          const uint64_t da = umma_smem_desc(sa + j * a_kstep, a_lbo, a_sbo, a_lt);
-          const uint64_t db = umma_smem_desc(sb + j * b_kstep, b_lbo, b_sbo, b_lt);
-          const uint32_t acc = (it > 0 || j > 0) ? 1u : 0u;
-          if (NSPLIT == 3) {
-            const uint64_t da_t = umma_smem_desc(sa + tail_off + j * a_kstep, a_lbo, a_sbo, a_lt);
-            const uint64_t db_t = umma_smem_desc(sb + tail_off + j * b_kstep, b_lbo, b_sbo, b_lt);
-            umma_tf32_ss(tmem_base, da_t, db, idesc, acc);  // small terms first
-            umma_tf32_ss(tmem_base, da, db_t, idesc, 1u);
-            umma_tf32_ss(tmem_base, da, db, idesc, 1u);
+        const uint32_t tmem_acc = tmem_base + static_cast<uint32_t>(buf) * MAX_BN;
+        for (int it = 0; it < n_iters; ++it) {
+          mbar_wait(NSPLIT == 3 ? &ready_bar[s] : &full_bar[s], ph);
+          tcgen05_fence_after();
+          const uint32_t sa = ring + static_cast<uint32_t>(s) * p.stage_bytes;
+          const uint32_t sb = sa + p.a_bytes;
+          if (p.debug & 2) {
+            mbar_arrive(&empty_bar[s]);
           } else {
-            umma_tf32_ss(tmem_base, da, db, idesc, acc);
+            const int k_left = p.K - (kb_begin + it) * BK;
+            const int ksteps = min(BK / UMMA_K, (k_left + UMMA_K - 1) / UMMA_K);
+            for (int k = 0; k < ksteps; ++k) {
+              const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, a_sbo, a_lt);
+              const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, b_sbo, b_lt);
+              const uint32_t acc = (it > 0 || k > 0) ? 1u : 0u;
+              if (NSPLIT == 3) {
+                const uint64_t da_t = umma_smem_desc(sa + tail_off + k * a_kstep, a_lbo, a_sbo, a_lt);
+                const uint64_t db_t = umma_smem_desc(sb + tail_off + k * b_kstep, b_lbo, b_sbo, b_lt);
+                umma_tf32_ss(tmem_acc, da_t, db, idesc, acc);  // small terms first
+                umma_tf32_ss(tmem_acc, da, db_t, idesc, 1u);
+                umma_tf32_ss(tmem_acc, da, db, idesc, 1u);
+              } else {
+                umma_tf32_ss(tmem_acc, da, db, idesc, acc);
+              }
+            }
+            tcgen05_commit(&empty_bar[s]);  // smem slot reusable once these MMAs have read it
           }
+          if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
-        tcgen05_commit(&empty_bar[s]);  // smem slot reusable once these MMAs have read it
+        if (p.debug & 2) mbar_arrive(&tmem_full_bar[buf]);
+        else tcgen05_commit(&tmem_full_bar[buf]);  // accumulators of this unit complete
+        if (stamps && j == 0) stamps[2] = clock64();
       }
-      if (p.debug & 2) mbar_arrive(&accum_bar);
-      else tcgen05_commit(&accum_bar);  // accumulators complete
-      if (stamps) stamps[2] = clock64();
     }
     __syncwarp();
-  } else {
-    // ------------------------------------------------------------------ splitter, then epilogue
-    const int et = threadIdx.x - 64;  // 0..127
-    // bias slice of this tile -> smem once (zero beyond N), read back as warp-wide broadcasts
-    for (int j = et; j < MAX_BN; j += EPI_THREADS)
-      s_bias[j] = (p.bias != nullptr && j < p.bn && n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
-    named_bar_sync(1, EPI_THREADS);
+  } else if (warp < 2 + SPLIT_THREADS / 32) {
+    // ------------------------------------------------------------------ splitters (3xTF32 only)
     if (NSPLIT == 3) {
+      const int st = threadIdx.x - 64;  // 0..127
       const uint32_t raw_bytes = p.a_bytes + p.b_bytes;
       const int nvec = static_cast<int>(raw_bytes >> 4);
-      for (int it = 0; it < n_iters; ++it) {
-        const int s = it % p.stages;
-        const uint32_t ph = (it / p.stages) & 1;
-        mbar_wait(&full_bar[s], ph);
-        const float4* raw = reinterpret_cast<const float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes);
-        float4* tail = reinterpret_cast<float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes + raw_bytes);
-#pragma unroll 4
-        for (int i = et; i < nvec; i += EPI_THREADS) {
-          const float4 v = raw[i];
-          float4 t;
-          t.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u);
-          t.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u);
-          t.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u);
-          t.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u);
-          tail[i] = t;
-        }
-        fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor core's async proxy
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&ready_bar[s]);
-      }
-    }
-
-    if (stamps && et == 0) stamps[1] = clock64();
-    mbar_wait(&accum_bar, 0);
-    tcgen05_fence_after();
-    if (stamps && et == 0) stamps[3] = clock64();
-
-    const int wq = warp & 3;                 // TMEM lane quarter this warp may read
-    const int r_in_tile = wq * 32 + lane;
-    const int row = m0 + r_in_tile;
-    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(wq * 32) << 16);
-    const int n_cols_out = min(p.bn, p.n_store - n0);  // columns to write (valid + zero padding)
-    const int n_chunks = (n_cols_out + 31) / 32;
-    const int acc_chunks = (static_cast<int>(umma_n) + 31) / 32;  // chunks that hold MMA output
-    uint32_t r[32];
-
-    bool finalize = true;
-    if (p.splits > 1) {
-      // split-K: park this split's partial tile in scratch; splitk_reduce_kernel sums the splits in
-      // order (deterministic) and applies the epilogue
-      float* my = p.scratch + (static_cast<size_t>(tile) * p.splits + split) * (BM * MAX_BN);
-      for (int c = 0; c < acc_chunks; ++c) {
-        tmem_ld_32x32(taddr + c * 32, r);
-        tmem_ld_wait();
-        float4* dst = reinterpret_cast<float4*>(my + (static_cast<size_t>(c) * BM + r_in_tile) * 32);
+      int s = 0;
+      uint32_t ph = 0;
+      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
+        const int split = u / tiles;
+        const int kb_begin = split * p.kb_per_split;
+        const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
+        for (int it = 0; it < n_iters; ++it) {
+          mbar_wait(&full_bar[s], ph);
+          const float4* raw = reinterpret_cast<const float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes);
+          float4* tail = reinterpret_cast<float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes + raw_bytes);
+          // SPLIT_ILP loads are issued back to back before any store: the compiler cannot prove that the
+          // tail tile does not alias the raw tile, so a plain loop serialises LDS -> STS -> LDS.
+          constexpr int SPLIT_ILP = 6;
+          for (int base = st; base < ((p.debug & 8) ? 0 : nvec); base += SPLIT_THREADS * SPLIT_ILP) {
+            float4 v[SPLIT_ILP];
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-          dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
-                               __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+            for (int q = 0; q < SPLIT_ILP; ++q) {
+              const int i = base + q * SPLIT_THREADS;
+              if (i < nvec) v[q] = raw[i];
+            }
+#pragma unroll
+            for (int q = 0; q < SPLIT_ILP; ++q) {
+              const int i = base + q * SPLIT_THREADS;
+              if (i < nvec) {
+                float4 t;
+                t.x = v[q].x - __uint_as_float(__float_as_uint(v[q].x) & 0xFFFFE000u);
+                t.y = v[q].y - __uint_as_float(__float_as_uint(v[q].y) & 0xFFFFE000u);
+                t.z = v[q].z - __uint_as_float(__float_as_uint(v[q].z) & 0xFFFFE000u);
+                t.w = v[q].w - __uint_as_float(__float_as_uint(v[q].w) & 0xFFFFE000u);
+                tail[i] = t;
+              }
+            }
+          }
+          fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor core's async proxy
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&ready_bar[s]);
+          if (++s == p.stages) { s = 0; ph ^= 1u; }
+        }
       }
-      finalize = false;
     }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps
+    const int et = threadIdx.x - (64 + SPLIT_THREADS);  // 0..127
+    const int wq = warp & 3;                            // TMEM lane quarter this warp may read
+    const int r_in_tile = wq * 32 + lane;
+    const bool has_drop = p.drop_thr16 != 0u;
+    const bool has_mask = p.mask_src != nullptr;
+    const bool relu = p.relu != 0;
+    uint32_t step = p.step_imm;
+    if (has_drop && p.step_ptr != nullptr) step = *p.step_ptr;
+    uint8_t* stage_buf = staging + static_cast<size_t>(wq) * 8192;   // two 32x32 fp32 boxes per warp
+    uint32_t stores_issued = 0;
+    uint32_t r[32];
+    int j = 0;
+    for (int u = blockIdx.x; u < total_units; u += gridDim.x, ++j) {
+      const int tile = u % tiles, split = u / tiles;
+      const int m0 = (tile % p.m_tiles) * BM, n0 = (tile / p.m_tiles) * p.bn;
+      const int n_valid = min(p.bn, p.N - n0);
+      const int umma_n = min(p.bn, (n_valid + 15) & ~15);
+      const int row = m0 + r_in_tile;
+      const int buf = j & 1;
+      const uint32_t taddr = tmem_base + static_cast<uint32_t>(buf) * MAX_BN + (static_cast<uint32_t>(wq * 32) << 16);
+      const int n_cols_out = min(p.bn, p.n_store - n0);  // columns to write (valid + zero padding)
+      const int n_chunks = (n_cols_out + 31) / 32;
+      const int acc_chunks = (umma_n + 31) / 32;         // chunks that hold MMA output
 
-    if (finalize) {
-      const bool has_drop = p.drop_thr16 != 0u;
-      const bool has_mask = p.mask_src != nullptr;
-      const bool relu = p.relu != 0;
-      uint32_t step = p.step_imm;
-      if (has_drop && p.step_ptr != nullptr) step = *p.step_ptr;
-      // TMA-store staging: two 32x32 fp32 boxes per warp at the start of the (now idle) stage ring
-      uint8_t* stage_buf = ring_ptr + static_cast<size_t>(wq) * 8192;
+      // bias slice of this tile -> smem (zero beyond N); the barrier also fences the previous unit's reads
+      named_bar_sync(1, EPI_THREADS);
+      for (int c = et; c < MAX_BN; c += EPI_THREADS)
+        s_bias[c] = (p.bias != nullptr && c < p.bn && n0 + c < p.N) ? __ldg(p.bias + n0 + c) : 0.f;
+      named_bar_sync(1, EPI_THREADS);
+
+      mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);
+      tcgen05_fence_after();
+
+      if (p.splits > 1) {
+        // split-K: park this split's partial tile in scratch; splitk_reduce_kernel sums the splits in
+        // order (deterministic) and applies the epilogue
+        float* my = p.scratch + (static_cast<size_t>(tile) * p.splits + split) * (BM * MAX_BN);
+        for (int c = 0; c < acc_chunks; ++c) {
+          tmem_ld_32x32(taddr + c * 32, r);
+          tmem_ld_wait();
+          float4* dst = reinterpret_cast<float4*>(my + (static_cast<size_t>(c) * BM + r_in_tile) * 32);
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                                 __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
+        continue;
+      }
+
       for (int c = 0; c < n_chunks; ++c) {
         float v[32];
         if (c < acc_chunks) {
           tmem_ld_32x32(taddr + c * 32, r);
           tmem_ld_wait();
         }
+        if (c == acc_chunks - 1 || (acc_chunks == 0 && c == 0)) {
+          // last TMEM read of this unit: hand the accumulator buffer back to the MMA warp
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
+        }
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = (c < acc_chunks) ? __uint_as_float(r[j]) : 0.f;
+        for (int q = 0; q < 32; ++q) v[q] = (c < acc_chunks) ? __uint_as_float(r[q]) : 0.f;
         // TMEM columns past the MMA's N were never written: force them (and their bias) to zero.
         // Columns between N and umma_n hold exact zeros already (TMA zero-fills out-of-range B rows).
-        const int live = static_cast<int>(umma_n) - c * 32;
+        const int live = umma_n - c * 32;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float x = (j < live) ? v[j] + s_bias[c * 32 + j] : 0.f;
-          v[j] = relu ? fmaxf(x, 0.f) : x;
+        for (int q = 0; q < 32; ++q) {
+          float x = (q < live) ? v[q] + s_bias[c * 32 + q] : 0.f;
+          v[q] = relu ? fmaxf(x, 0.f) : x;
         }
         const int col0 = n0 + c * 32;
         // dropout: element index e = row*N + col, 8 elements per Philox call, 16 bits each
@@ -289,16 +349,16 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               const Philox4 rnd = philox4x32_10(static_cast<uint32_t>(grp), static_cast<uint32_t>(grp >> 32), step,
                                                 p.salt, p.seed_lo, p.seed_hi);
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
-                v[g * 8 + j] = (rand16(rnd, j) >= p.drop_thr16) ? v[g * 8 + j] * p.drop_scale : 0.f;
+              for (int q = 0; q < 8; ++q)
+                v[g * 8 + q] = (rand16(rnd, q) >= p.drop_thr16) ? v[g * 8 + q] * p.drop_scale : 0.f;
             } else {
               // unaligned row start (N not a multiple of 8): one Philox call per element group it touches
-              for (int j = 0; j < 8; ++j) {
-                const unsigned long long e = e0 + j;
+              for (int q = 0; q < 8; ++q) {
+                const unsigned long long e = e0 + q;
                 const unsigned long long grp = e >> 3;
                 const Philox4 rnd = philox4x32_10(static_cast<uint32_t>(grp), static_cast<uint32_t>(grp >> 32),
                                                   step, p.salt, p.seed_lo, p.seed_hi);
-                v[g * 8 + j] = (rand16(rnd, static_cast<int>(e & 7ull)) >= p.drop_thr16) ? v[g * 8 + j] * p.drop_scale
+                v[g * 8 + q] = (rand16(rnd, static_cast<int>(e & 7ull)) >= p.drop_thr16) ? v[g * 8 + q] * p.drop_scale
                                                                                        : 0.f;
               }
             }
@@ -320,29 +380,30 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
           } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < p.N) v[j] = (__ldg(ms + j) > 0.f) ? v[j] * p.mask_scale : 0.f;
+            for (int q = 0; q < 32; ++q)
+              if (col0 + q < p.N) v[q] = (__ldg(ms + q) > 0.f) ? v[q] * p.mask_scale : 0.f;
           }
         }
         if (p.debug & 4) continue;
         if (p.tma_store) {
           // registers -> 128B-swizzled smem box -> one bulk tensor store per warp (clipped at the
           // tensor edge by the TMA unit, full 128-byte lines on the wire)
-          uint8_t* buf = stage_buf + (c & 1) * 4096;
-          if (c >= 2) {
-            if (lane == 0) tma_store_wait_read<1>();  // the store issued two chunks ago has drained this box
+          uint8_t* box = stage_buf + (stores_issued & 1u) * 4096;
+          if (stores_issued >= 2) {
+            if (lane == 0) tma_store_wait_read<1>();  // the store issued two boxes ago has drained this one
             __syncwarp();
           }
-          uint8_t* rowp = buf + lane * 128;
+          uint8_t* rowp = box + lane * 128;
 #pragma unroll
           for (int q = 0; q < 8; ++q)
             *reinterpret_cast<float4*>(rowp + ((q ^ (lane & 7)) << 4)) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&tmOut, buf, col0, m0 + wq * 32);
+            tma_store_2d(&tmOut, box, col0, m0 + wq * 32);
             tma_store_commit();
           }
+          ++stores_issued;
         } else if (row < p.M) {
           float* dst = p.out + static_cast<size_t>(row) * p.ldo + col0;
           const int rem = n_cols_out - c * 32;
@@ -352,16 +413,15 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               reinterpret_cast<float4*>(dst)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
           } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (j < rem) dst[j] = v[j];
+            for (int q = 0; q < 32; ++q)
+              if (q < rem) dst[q] = v[q];
           }
         }
       }
-      if (p.tma_store && lane == 0) tma_store_wait_all();  // smem must outlive the bulk reads
     }
+    if (p.tma_store && lane == 0) tma_store_wait_all();  // smem must outlive the bulk reads
   }
 
-  if (stamps && threadIdx.x == 64) stamps[4] = clock64();
   // teardown: all TMEM reads done before the allocating warp frees the columns
   tcgen05_fence_before();
   __syncthreads();
@@ -486,14 +546,12 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
   pl->a_bytes = BM * pl->bk * 4;
   pl->b_bytes = static_cast<uint32_t>(bn) * pl->bk * 4;
   pl->stage_bytes = (pl->a_bytes + pl->b_bytes) * (d->precision == 3 ? 2u : 1u);
-  int stages = static_cast<int>((SMEM_LIMIT - STATIC_SMEM_RESERVE - 1024) / pl->stage_bytes);
+  int stages = static_cast<int>((SMEM_LIMIT - STATIC_SMEM_RESERVE - 1024 - EPI_STAGING_BYTES) / pl->stage_bytes);
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages > pl->num_kb) stages = pl->num_kb < 1 ? 1 : pl->num_kb;
   if (stages < 1) return fail(RTDC_ERR_LIMIT, "tile does not fit shared memory");
   pl->stages = stages;
-  pl->smem = static_cast<size_t>(stages) * pl->stage_bytes;
-  if (pl->smem < 32768) pl->smem = 32768;  // the epilogue stages its TMA stores in the idle ring (4 warps x 8 KB)
-  pl->smem += 1024;
+  pl->smem = static_cast<size_t>(stages) * pl->stage_bytes + EPI_STAGING_BYTES + 1024;
   const int tiles = pl->m_tiles * pl->n_tiles;
   int splits = d->splits;
   if (splits == 0) {
@@ -525,7 +583,8 @@ template <bool A_MN, bool B_MN, int NSPLIT, int BK>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const GemmParams& gp, const Plan& pl, cudaStream_t st) {
   auto kern = gemm_tf32_kernel<A_MN, B_MN, NSPLIT, BK>;
   RTDC_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT - STATIC_SMEM_RESERVE));
-  dim3 grid(pl.m_tiles * pl.n_tiles, pl.splits, 1);
+  const int units = pl.m_tiles * pl.n_tiles * pl.splits;
+  const int grid = units < num_sms() ? units : num_sms();   // persistent: one CTA per SM walks the work units
   kern<<<grid, NUM_THREADS, pl.smem, st>>>(ta, tb, to, gp);
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;

@@ -20,7 +20,12 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
 }
 
 // Every device-side wait in this library is bounded: a protocol bug must trap (the launch then
-// fails with an error the host sees) instead of hanging the GPU.
+// fails with an error the host sees) instead of hanging the GPU. The bound is counted in SM clock
+// cycles (clock64 is a cheap register read; %globaltimer costs hundreds of cycles per read and must
+// stay out of wait loops).
+#ifndef RTDC_WAIT_TIMEOUT_CYCLES
+#define RTDC_WAIT_TIMEOUT_CYCLES 8000000000ll  /* ~4 s at 2 GHz */
+#endif
 #ifndef RTDC_WAIT_TIMEOUT_NS
 #define RTDC_WAIT_TIMEOUT_NS 4000000000ull
 #endif
@@ -52,9 +57,9 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  const uint64_t t0 = global_timer_ns();
+  const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
-    if (global_timer_ns() - t0 > RTDC_WAIT_TIMEOUT_NS) {
+    if (clock64() - t0 > RTDC_WAIT_TIMEOUT_CYCLES) {
       printf("rtdc: mbarrier wait timed out (block %d,%d thread %d)\n", blockIdx.x, blockIdx.y, threadIdx.x);
       __trap();
     }

@@ -165,8 +165,9 @@ class U8BatchLoader:
 
     def __init__(self, images_u8: torch.Tensor, labels: torch.Tensor, batch_size: int, device, *, shuffle: bool = True,
                  world: int = 1, rank: int = 0, seed: int = 0, drop_last: bool = True, normalize: bool = False,
-                 mean: float = 0.5, std: float = 0.5, lookahead: int = 2):
+                 mean: float = 0.5, std: float = 0.5, lookahead: int = 2, prefetch_next_epoch: bool = True):
         assert images_u8.dtype == torch.uint8 and labels.dtype == torch.int64
+        self.prefetch_next_epoch = prefetch_next_epoch
         self.images = images_u8.reshape(images_u8.shape[0], -1).contiguous()
         self.labels = labels.contiguous()
         self.row = self.images.shape[1]
@@ -226,7 +227,7 @@ class U8BatchLoader:
         hx, hy = self._host_x[slot], self._host_y[slot]
         nb, bs = len(self), self.batch_size
         total = len(self.sampler)
-        if nb > 1:
+        if nb > 1 and self.prefetch_next_epoch:
             self._prepare(epoch + 1)            # next epoch's shuffle overlaps this epoch's training
         if not self.cuda:
             for i in range(nb):

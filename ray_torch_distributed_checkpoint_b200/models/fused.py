@@ -54,13 +54,19 @@ class _FusedLinearActFn(torch.autograd.Function):
         else:
             dz = dy2
         dz = dz.contiguous()
+        n_out = dz.shape[1]
+        if n_out % 4 != 0:
+            # TMA needs a 16-byte row pitch: pad e.g. the 10-wide logit gradient to 12 columns of zeros
+            dz_p = torch.zeros(dz.shape[0], (n_out + 3) // 4 * 4, device=dz.device, dtype=dz.dtype)
+            dz_p[:, :n_out] = dz
+            dz = dz_p
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            dx = ops.linear_dgrad(dz, weight, precision=ctx.precision).reshape(ctx.x_shape)
+            dx = ops.linear_dgrad(dz, weight, N_out=n_out, precision=ctx.precision).reshape(ctx.x_shape)
         if ctx.needs_input_grad[1]:
-            dw = ops.linear_wgrad(dz, x2, precision=ctx.precision)
+            dw = ops.linear_wgrad(dz, x2, N_out=n_out, precision=ctx.precision)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = ops.colsum(dz)
+            db = ops.colsum(dz, cols=n_out)
         return dx, dw, db, None, None, None, None, None, None
 
 

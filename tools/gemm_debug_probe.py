@@ -1,8 +1,8 @@
-"""Component timing of the GEMM kernel with RTDC_GEMM_DEBUG bits (1 no TMA, 2 no MMA, 4 no stores)."""
-import os, sys, json
+"""Component timing of the GEMM kernel with RTDC_GEMM_DEBUG bits (1 no TMA, 2 no MMA, 4 no stores, 8 no split, 16 no fence)."""
+import os, sys
 import torch
 from ray_torch_distributed_checkpoint_b200 import ops
-B = 16384
+B = 18944
 dev = "cuda"
 x = torch.randn(B, 784, device=dev); w1 = torch.randn(512, 784, device=dev) * .03; b1 = torch.randn(512, device=dev)
 out = torch.empty(B, 512, device=dev)
@@ -18,9 +18,7 @@ def t(fn, n=10):
         g.replay(); s.synchronize()
         a.record(s); g.replay(); b.record(s); s.synchronize()
     return a.elapsed_time(b) / n * 1000
-for prec in (1, 3):
-    for bn in (256, 128):
-        for dbg in (0, 1, 2, 4, 5, 6, 3):
-            os.environ["RTDC_GEMM_DEBUG"] = str(dbg)
-            us = t(lambda: ops.gemm(x, w1, out, bias=b1, relu=True, precision=prec, bn=bn))
-            print(f"prec={prec} bn={bn} debug={dbg}: {us:.1f} us", flush=True)
+for dbg in (0, 8, 2, 10, 1, 3, 11):
+    os.environ["RTDC_GEMM_DEBUG"] = str(dbg)
+    us = t(lambda: ops.gemm(x, w1, out, bias=b1, relu=True, precision=3))
+    print(f"fwd1 prec=3 B={B} debug={dbg}: {us:.1f} us", flush=True)
