@@ -70,13 +70,14 @@ int rtdc_gemm_plan(const rtdc_gemm_desc* d, int* out5);
  * labels int64 [rows]. Writes the mean loss (sum/rows, ref: nn.CrossEntropyLoss() default,
  * my_ray_module.py:141,156), optionally dlogits [rows, ldz] = (softmax - onehot) * grad_scale,
  * multiplied by (logit > 0) when relu_mask != 0 (the reference's trailing ReLU, :106), padding
- * columns zeroed; optionally counts argmax==label into correct (ref: :170).
+ * columns zeroed; optionally counts argmax==label into correct (ref: :170); optionally writes the
+ * column sums of dlogits into dbias_out[classes] (the bias gradient of the layer that produced the logits).
  * scratch: rtdc_softmax_ce_scratch_bytes(rows) bytes, zero before first use, left zero after.
  */
 size_t rtdc_softmax_ce_scratch_bytes(int rows);
 int rtdc_softmax_ce(const float* logits, int ldz, const int64_t* labels, int rows, int classes,
                     float* loss_out, float* dlogits, float grad_scale, int relu_mask,
-                    unsigned long long* correct_accum, float* loss_sum_accum,
+                    unsigned long long* correct_accum, float* loss_sum_accum, float* dbias_out,
                     void* scratch, size_t scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------

@@ -21,18 +21,25 @@ struct CeScratch {
   unsigned int pad[63];
   float partial[CE_MAX_BLOCKS];
   unsigned long long correct[CE_MAX_BLOCKS];
+  float dbias[CE_MAX_BLOCKS][32];   // per-block column sums of dlogits (bias gradient of the last layer)
 };
 
 template <int MAXC>
 __global__ void __launch_bounds__(CE_THREADS)
 softmax_ce_kernel(const float* __restrict__ logits, int ldz, const long long* __restrict__ labels, int rows,
                   int classes, float* __restrict__ loss_out, float* __restrict__ dlogits, float grad_scale,
-                  int relu_mask, unsigned long long* correct_accum, float* loss_sum_accum, CeScratch* scratch) {
+                  int relu_mask, unsigned long long* correct_accum, float* loss_sum_accum, float* __restrict__ dbias_out,
+                  CeScratch* scratch) {
   __shared__ float s_loss[CE_THREADS / 32];
   __shared__ unsigned int s_correct[CE_THREADS / 32];
+  __shared__ float s_db[CE_THREADS / 32][32];
   __shared__ unsigned int s_last;
   float my_loss = 0.f;
   unsigned int my_correct = 0;
+  const bool want_db = dbias_out != nullptr && dlogits != nullptr;
+  float gsum[MAXC];
+#pragma unroll
+  for (int j = 0; j < MAXC; ++j) gsum[j] = 0.f;
   for (int row = blockIdx.x * blockDim.x + threadIdx.x; row < rows; row += gridDim.x * blockDim.x) {
     const float* z = logits + static_cast<size_t>(row) * ldz;
     float v[MAXC];
@@ -81,6 +88,7 @@ softmax_ce_kernel(const float* __restrict__ logits, int ldz, const long long* __
           if (relu_mask && !(v[j] > 0.f)) t = 0.f;
         }
         g[j] = t;
+        gsum[j] += t;
       }
       if ((ldz & 3) == 0) {
 #pragma unroll
@@ -100,31 +108,77 @@ softmax_ce_kernel(const float* __restrict__ logits, int ldz, const long long* __
     my_correct += __shfl_xor_sync(0xffffffffu, my_correct, o);
   }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (want_db) {
+#pragma unroll
+    for (int j = 0; j < MAXC; ++j) {
+      float t = gsum[j];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+      if (lane == 0) s_db[warp][j] = t;
+    }
+  }
   if (lane == 0) { s_loss[warp] = my_loss; s_correct[warp] = my_correct; }
   __syncthreads();
+  if (want_db && threadIdx.x < 32) {
+    float t = 0.f;
+    if (threadIdx.x < MAXC)
+      for (int w = 0; w < CE_THREADS / 32; ++w) t += s_db[w][threadIdx.x];
+    scratch->dbias[blockIdx.x][threadIdx.x] = t;
+  }
   if (threadIdx.x == 0) {
     float bl = 0.f;
     unsigned int bc = 0;
     for (int w = 0; w < CE_THREADS / 32; ++w) { bl += s_loss[w]; bc += s_correct[w]; }
     scratch->partial[blockIdx.x] = bl;
     scratch->correct[blockIdx.x] = bc;
-    __threadfence();
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
     const unsigned int old = atomicAdd(&scratch->counter, 1u);
     s_last = (old == gridDim.x - 1) ? 1u : 0u;
   }
   __syncthreads();
-  if (s_last && threadIdx.x == 0) {
+  if (s_last) {
+    // last block to finish: sum the per-block partials with all 256 threads (independent loads in
+    // flight), in an order that depends only on the grid size, so the result is reproducible
     __threadfence();
-    float total = 0.f;
-    unsigned long long corr = 0;
-    for (unsigned int b = 0; b < gridDim.x; ++b) {
-      total += __ldcg(&scratch->partial[b]);
-      corr += __ldcg(&scratch->correct[b]);
+    __shared__ float f_loss[CE_THREADS];
+    __shared__ unsigned long long f_corr[CE_THREADS];
+    float tl = 0.f;
+    unsigned long long tc = 0;
+    for (unsigned int b = threadIdx.x; b < gridDim.x; b += CE_THREADS) {
+      tl += __ldcg(&scratch->partial[b]);
+      tc += __ldcg(&scratch->correct[b]);
     }
-    if (loss_out) *loss_out = total / static_cast<float>(rows);
-    if (loss_sum_accum) *loss_sum_accum += total / static_cast<float>(rows);  // per-batch mean, summed (ref :168)
-    if (correct_accum) *correct_accum += corr;
-    scratch->counter = 0u;  // ready for the next launch
+    f_loss[threadIdx.x] = tl;
+    f_corr[threadIdx.x] = tc;
+    if (want_db) {
+      const int c = threadIdx.x & 31, part = threadIdx.x >> 5;
+      float t = 0.f;
+      for (unsigned int b = part; b < gridDim.x; b += CE_THREADS / 32) t += __ldcg(&scratch->dbias[b][c]);
+      s_db[part][c] = t;
+    }
+    __syncthreads();
+    for (int o = CE_THREADS / 2; o > 0; o >>= 1) {
+      if (threadIdx.x < o) {
+        f_loss[threadIdx.x] += f_loss[threadIdx.x + o];
+        f_corr[threadIdx.x] += f_corr[threadIdx.x + o];
+      }
+      __syncthreads();
+    }
+    if (want_db && threadIdx.x < classes && threadIdx.x < 32) {
+      float t = 0.f;
+      for (int w = 0; w < CE_THREADS / 32; ++w) t += s_db[w][threadIdx.x];
+      dbias_out[threadIdx.x] = t;
+    }
+    if (threadIdx.x == 0) {
+      const float total = f_loss[0];
+      if (loss_out) *loss_out = total / static_cast<float>(rows);
+      if (loss_sum_accum) *loss_sum_accum += total / static_cast<float>(rows);  // per-batch mean, summed (ref :168)
+      if (correct_accum) *correct_accum += f_corr[0];
+      scratch->counter = 0u;  // ready for the next launch
+    }
   }
 }
 
@@ -175,7 +229,7 @@ colsum_kernel(const float* __restrict__ x, int ld, int rows, int cols, float* __
   __syncthreads();
   if (warp == 0) {
     float4 t = s_acc[0][lane];
-    for (int w = 1; w < CS_THREADS / 32; ++w) {
+    for (int w = 1; w < WARPS; ++w) {
       const float4 u = s_acc[w][lane];
       t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
     }
@@ -188,18 +242,30 @@ colsum_kernel(const float* __restrict__ x, int ld, int rows, int cols, float* __
       s_last = (old == gridDim.y - 1) ? 1u : 0u;
       if (s_last) counters[cg] = 0u;
     }
-    __syncwarp();
-    if (s_last) {
-      __threadfence();
-      float4 tot = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (unsigned int s = 0; s < gridDim.y; ++s) {
-        const float4 u = __ldcg(reinterpret_cast<const float4*>(partial + (static_cast<size_t>(s) * gridDim.x + cg) * CS_COLS + lane * 4));
-        tot.x += u.x; tot.y += u.y; tot.z += u.z; tot.w += u.w;
+  }
+  __syncthreads();
+  if (s_last) {
+    // last block of this column group: every warp sums a strided subset of the slabs (loads independent),
+    // then warp 0 adds the eight subtotals in warp order -> same result for the same grid, every time
+    __threadfence();
+    float4 tot = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (unsigned int sl = warp; sl < gridDim.y; sl += WARPS) {
+      const float4 u = __ldcg(reinterpret_cast<const float4*>(partial + (static_cast<size_t>(sl) * gridDim.x + cg) * CS_COLS + lane * 4));
+      tot.x += u.x; tot.y += u.y; tot.z += u.z; tot.w += u.w;
+    }
+    __syncthreads();
+    s_acc[warp][lane] = tot;
+    __syncthreads();
+    if (warp == 0) {
+      float4 t = s_acc[0][lane];
+      for (int w = 1; w < WARPS; ++w) {
+        const float4 u = s_acc[w][lane];
+        t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
       }
-      if (c0 < cols) out[c0] = tot.x;
-      if (c0 + 1 < cols) out[c0 + 1] = tot.y;
-      if (c0 + 2 < cols) out[c0 + 2] = tot.z;
-      if (c0 + 3 < cols) out[c0 + 3] = tot.w;
+      if (c0 < cols) out[c0] = t.x;
+      if (c0 + 1 < cols) out[c0 + 1] = t.y;
+      if (c0 + 2 < cols) out[c0 + 2] = t.z;
+      if (c0 + 3 < cols) out[c0 + 3] = t.w;
     }
   }
 }
@@ -210,18 +276,26 @@ u8_normalize_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst, si
   // 16 pixels per thread per iteration: one 128-bit load, four 128-bit stores
   const size_t nvec = n / 16;
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
-  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
-    const uint4 w = __ldg(reinterpret_cast<const uint4*>(src) + i);
-    const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
-    float4* o = reinterpret_cast<float4*>(dst) + i * 4;
+  for (size_t i0 = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < nvec; i0 += 2 * stride) {
+    const size_t idx[2] = {i0, i0 + stride};
+    uint4 w[2];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      float4 f;
-      f.x = static_cast<float>(ws[q] & 0xFFu) * scale + shift;
-      f.y = static_cast<float>((ws[q] >> 8) & 0xFFu) * scale + shift;
-      f.z = static_cast<float>((ws[q] >> 16) & 0xFFu) * scale + shift;
-      f.w = static_cast<float>(ws[q] >> 24) * scale + shift;
-      o[q] = f;
+    for (int u = 0; u < 2; ++u)
+      if (idx[u] < nvec) w[u] = __ldg(reinterpret_cast<const uint4*>(src) + idx[u]);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (idx[u] >= nvec) continue;
+      const uint32_t ws[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
+      float4* o = reinterpret_cast<float4*>(dst) + idx[u] * 4;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float4 f;
+        f.x = static_cast<float>(ws[q] & 0xFFu) * scale + shift;
+        f.y = static_cast<float>((ws[q] >> 8) & 0xFFu) * scale + shift;
+        f.z = static_cast<float>((ws[q] >> 16) & 0xFFu) * scale + shift;
+        f.w = static_cast<float>(ws[q] >> 24) * scale + shift;
+        o[q] = f;
+      }
     }
   }
   if (blockIdx.x == 0) {
@@ -331,7 +405,7 @@ RTDC_API size_t rtdc_softmax_ce_scratch_bytes(int) { return sizeof(CeScratch); }
 
 RTDC_API int rtdc_softmax_ce(const float* logits, int ldz, const int64_t* labels, int rows, int classes,
                              float* loss_out, float* dlogits, float grad_scale, int relu_mask,
-                             unsigned long long* correct_accum, float* loss_sum_accum, void* scratch,
+                             unsigned long long* correct_accum, float* loss_sum_accum, float* dbias_out, void* scratch,
                              size_t scratch_bytes, void* stream) {
   if (!logits || !labels || rows <= 0) return fail(RTDC_ERR_ARG, "logits/labels null or rows <= 0");
   if (classes < 1 || classes > 32 || ldz < classes) return fail(RTDC_ERR_LIMIT, "softmax_ce supports 1..32 classes with ldz >= classes (got %d, ldz %d)", classes, ldz);
@@ -340,9 +414,9 @@ RTDC_API int rtdc_softmax_ce(const float* logits, int ldz, const int64_t* labels
   const int blocks = grid_for(static_cast<size_t>(rows), CE_THREADS, 8);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (classes <= 16 && ldz <= 16)
-    softmax_ce_kernel<16><<<blocks, CE_THREADS, 0, st>>>(logits, ldz, reinterpret_cast<const long long*>(labels), rows, classes, loss_out, dlogits, grad_scale, relu_mask, correct_accum, loss_sum_accum, static_cast<CeScratch*>(scratch));
+    softmax_ce_kernel<16><<<blocks, CE_THREADS, 0, st>>>(logits, ldz, reinterpret_cast<const long long*>(labels), rows, classes, loss_out, dlogits, grad_scale, relu_mask, correct_accum, loss_sum_accum, dbias_out, static_cast<CeScratch*>(scratch));
   else
-    softmax_ce_kernel<32><<<blocks, CE_THREADS, 0, st>>>(logits, ldz, reinterpret_cast<const long long*>(labels), rows, classes, loss_out, dlogits, grad_scale, relu_mask, correct_accum, loss_sum_accum, static_cast<CeScratch*>(scratch));
+    softmax_ce_kernel<32><<<blocks, CE_THREADS, 0, st>>>(logits, ldz, reinterpret_cast<const long long*>(labels), rows, classes, loss_out, dlogits, grad_scale, relu_mask, correct_accum, loss_sum_accum, dbias_out, static_cast<CeScratch*>(scratch));
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;
 }

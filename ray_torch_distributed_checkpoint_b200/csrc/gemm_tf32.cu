@@ -445,9 +445,15 @@ splitk_reduce_kernel(const float* __restrict__ scratch, int splits, int m_tiles,
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   const float* src = scratch + (static_cast<size_t>(tile) * splits) * (BM * MAX_BN) + (static_cast<size_t>(c) * BM + r) * 32 + q * 4;
   if (col < N) {
-    for (int z = 0; z < splits; ++z) {
-      const float4 t = __ldcg(reinterpret_cast<const float4*>(src + static_cast<size_t>(z) * (BM * MAX_BN)));
-      acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+    constexpr int ZI = 8;   // loads in flight; the sum is still formed in split order
+    for (int z0 = 0; z0 < splits; z0 += ZI) {
+      float4 t[ZI];
+#pragma unroll
+      for (int u = 0; u < ZI; ++u)
+        if (z0 + u < splits) t[u] = __ldcg(reinterpret_cast<const float4*>(src + static_cast<size_t>(z0 + u) * (BM * MAX_BN)));
+#pragma unroll
+      for (int u = 0; u < ZI; ++u)
+        if (z0 + u < splits) { acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w; }
     }
   }
   float v[4] = {acc.x, acc.y, acc.z, acc.w};

@@ -62,7 +62,7 @@ def _declare(lib):
     lib.rtdc_gemm_plan.argtypes = [C.POINTER(GemmDesc), C.POINTER(i * 5)]
     lib.rtdc_softmax_ce_scratch_bytes.argtypes = [i]
     lib.rtdc_softmax_ce_scratch_bytes.restype = sz
-    lib.rtdc_softmax_ce.argtypes = [vp, i, vp, i, i, vp, vp, f, i, vp, vp, vp, sz, vp]
+    lib.rtdc_softmax_ce.argtypes = [vp, i, vp, i, i, vp, vp, f, i, vp, vp, vp, vp, sz, vp]
     lib.rtdc_colsum_scratch_bytes.argtypes = [i, i]
     lib.rtdc_colsum_scratch_bytes.restype = sz
     lib.rtdc_colsum.argtypes = [vp, i, i, i, vp, vp, sz, vp]

@@ -21,11 +21,12 @@ def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor, *, classes
                           dlogits: Optional[torch.Tensor] = None, grad_scale: Optional[float] = None,
                           relu_mask: bool = False, loss_out: Optional[torch.Tensor] = None,
                           correct_accum: Optional[torch.Tensor] = None, loss_sum_accum: Optional[torch.Tensor] = None,
-                          stream=None) -> torch.Tensor:
+                          dbias_out: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
     """Mean cross-entropy of ``logits[:, :classes]``; optionally also writes
     ``dlogits = (softmax - onehot) * grad_scale`` (default ``1/rows``), masked by ``logits > 0`` when
     ``relu_mask`` (the reference model ends in a ReLU), and accumulates the number of correct
-    argmax predictions into ``correct_accum`` (uint64/int64 scalar on the device)."""
+    argmax predictions into ``correct_accum`` (uint64/int64 scalar on the device). ``dbias_out[classes]``
+    receives the column sums of ``dlogits`` (bias gradient of the logit layer) from the same pass."""
     if logits.dtype != torch.float32 or not logits.is_cuda or logits.dim() != 2 or logits.stride(1) != 1:
         raise ValueError("logits must be a 2-D float32 CUDA tensor with unit inner stride")
     if labels.dtype != torch.int64 or not labels.is_contiguous():
@@ -44,6 +45,7 @@ def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor, *, classes
         dlogits.data_ptr() if dlogits is not None else None, gs, int(relu_mask),
         correct_accum.data_ptr() if correct_accum is not None else None,
         loss_sum_accum.data_ptr() if loss_sum_accum is not None else None,
+        dbias_out.data_ptr() if dbias_out is not None else None,
         ws.data_ptr(), ws.numel(), _lib.stream_ptr(stream)))
     return loss_out
 

@@ -155,10 +155,9 @@ class MLPTrainEngine:
         inv_keep = 1.0 / (1.0 - self.p_drop) if self.p_drop > 0 else 1.0
         n = self._forward(s, True, from_u8)
         ops.softmax_cross_entropy(self.z, self.y, classes=self.d_out, dlogits=self.dz, grad_scale=1.0 / B, relu_mask=True,
-                                  loss_out=self.loss, stream=s); n += 1
+                                  loss_out=self.loss, dbias_out=self.db[2], stream=s); n += 1   # also emits db3
         # layer 3
         ops.linear_wgrad(self.dz, self.h2, N_out=self.d_out, out=self.dW[2], precision=prec, stream=s); n += 2
-        ops.colsum(self.dz, cols=self.d_out, out=self.db[2], stream=s); n += 1
         ops.linear_dgrad(self.dz, self.W[2], N_out=self.d_out, mask_src=self.h2, mask_scale=inv_keep, out=self.dh2,
                          precision=prec, stream=s); n += 1
         # layer 2

@@ -20,7 +20,8 @@ def test_softmax_ce_forward_backward(rows):
     y = torch.randint(0, 10, (rows,), device="cuda", generator=g)
     dz = torch.full_like(z, 5.0)
     correct = torch.zeros((), dtype=torch.int64, device="cuda")
-    loss = ops.softmax_cross_entropy(z, y, classes=10, dlogits=dz, relu_mask=True, correct_accum=correct)
+    db = torch.full((10,), 7.0, device="cuda")
+    loss = ops.softmax_cross_entropy(z, y, classes=10, dlogits=dz, relu_mask=True, correct_accum=correct, dbias_out=db)
     zr = z[:, :10].clone().requires_grad_(True)
     ref = F.cross_entropy(zr, y)
     ref.backward()
@@ -28,6 +29,7 @@ def test_softmax_ce_forward_backward(rows):
     ref_dz = zr.grad * (z[:, :10] > 0)
     assert torch.allclose(dz[:, :10], ref_dz, rtol=1e-4, atol=1e-7 / max(rows, 1) + 1e-9)
     assert (dz[:, 10:] == 0).all()
+    assert torch.allclose(db.double(), dz[:, :10].double().sum(0), rtol=1e-4, atol=1e-6)      # fused bias gradient
     assert correct.item() == (z[:, :10].argmax(1) == y).sum().item()
     # determinism + accumulation on a second launch
     loss2 = ops.softmax_cross_entropy(z, y, classes=10, correct_accum=correct)
