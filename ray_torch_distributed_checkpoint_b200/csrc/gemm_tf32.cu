@@ -28,7 +28,7 @@ constexpr int BM = 128;           // tile rows == TMEM lanes
 // K block (fp32 elements per pipeline stage): 32 = one 128-byte swizzle row, 16 = one 64-byte row.
 // 3xTF32 uses 16 so that four stages (raw + tail tiles) fit in shared memory.
 constexpr int UMMA_K = 8;         // tf32: 32 bytes per instruction along K
-constexpr int MAX_STAGES = 4;
+constexpr int MAX_STAGES = 6;
 constexpr int MAX_BN = 256;
 constexpr int TMEM_COLS = 512;      // two 256-column accumulator buffers (epilogue of one tile overlaps the next main loop)
 constexpr int NUM_THREADS = 320;    // 10 warps: 0 TMA producer, 1 MMA issuer, 2-5 splitters, 6-9 epilogue
@@ -42,6 +42,7 @@ struct GemmParams {
   int M, N, K;
   int bn, stages, splits, kb_per_split, num_kb;
   int m_tiles, n_tiles;
+  int m_tiles2;   // 256-row tiles (CTA-pair kernel)
   uint32_t a_bytes, b_bytes, stage_bytes;  // per stage: raw A, raw B, total (incl. tails when split)
   float* out; int ldo; int n_store;
   const float* bias; int relu;
@@ -57,6 +58,146 @@ struct GemmParams {
 __device__ __forceinline__ uint32_t rand16(const Philox4& r, int j) {
   const uint32_t w = (j < 2) ? r.x : (j < 4) ? r.y : (j < 6) ? r.z : r.w;
   return (j & 1) ? (w >> 16) : (w & 0xFFFFu);
+}
+
+// Epilogue of one work unit, run by the four epilogue warps: TMEM -> registers -> (+bias, ReLU, dropout,
+// backward mask) -> swizzled smem box -> TMA store (or split-K partial to scratch). `release()` hands the
+// accumulator buffer back to the MMA issuer right after this warp's last TMEM read.
+template <class ReleaseFn>
+__device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtensorMap* tmOut, uint32_t taddr, int umma_n,
+                                              int tile, int split, int m0, int n0, int r_in_tile, int lane, int wq,
+                                              const float* s_bias, uint8_t* stage_buf, uint32_t& stores_issued,
+                                              uint32_t step, ReleaseFn release) {
+  const bool has_drop = p.drop_thr16 != 0u;
+  const bool has_mask = p.mask_src != nullptr;
+  const bool relu = p.relu != 0;
+  const int row = m0 + r_in_tile;
+  const int n_cols_out = min(p.bn, p.n_store - n0);  // columns to write (valid + zero padding)
+  const int n_chunks = (n_cols_out + 31) / 32;
+  const int acc_chunks = (umma_n + 31) / 32;         // chunks that hold MMA output
+  uint32_t r[32];
+  if (p.splits > 1) {
+    // split-K: park this split's partial tile in scratch; splitk_reduce_kernel sums the splits in
+    // order (deterministic) and applies the epilogue
+    float* my = p.scratch + (static_cast<size_t>(tile < 0 ? 0 : tile) * p.splits + split) * (BM * MAX_BN);
+    for (int c = 0; c < (tile < 0 ? 0 : acc_chunks); ++c) {
+      tmem_ld_32x32(taddr + c * 32, r);
+      tmem_ld_wait();
+      float4* dst = reinterpret_cast<float4*>(my + (static_cast<size_t>(c) * BM + r_in_tile) * 32);
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                             __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+    }
+    tcgen05_fence_before();
+    __syncwarp();
+    release();
+    return;
+  }
+
+  for (int c = 0; c < n_chunks; ++c) {
+    float v[32];
+    if (c < acc_chunks) {
+      tmem_ld_32x32(taddr + c * 32, r);
+      tmem_ld_wait();
+    }
+    if (c == acc_chunks - 1 || (acc_chunks == 0 && c == 0)) {
+      // last TMEM read of this unit: hand the accumulator buffer back to the MMA warp
+      tcgen05_fence_before();
+      __syncwarp();
+      release();
+    }
+#pragma unroll
+    for (int q = 0; q < 32; ++q) v[q] = (c < acc_chunks) ? __uint_as_float(r[q]) : 0.f;
+    // TMEM columns past the MMA's N were never written: force them (and their bias) to zero.
+    // Columns between N and umma_n hold exact zeros already (TMA zero-fills out-of-range B rows).
+    const int live = umma_n - c * 32;
+#pragma unroll
+    for (int q = 0; q < 32; ++q) {
+      float x = (q < live) ? v[q] + s_bias[c * 32 + q] : 0.f;
+      v[q] = relu ? fmaxf(x, 0.f) : x;
+    }
+    const int col0 = n0 + c * 32;
+    // dropout: element index e = row*N + col, 8 elements per Philox call, 16 bits each
+    if (has_drop && row < p.M) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const unsigned long long e0 =
+            static_cast<unsigned long long>(row) * static_cast<unsigned long long>(p.N) + (col0 + g * 8);
+        if ((e0 & 7ull) == 0ull) {
+          const unsigned long long grp = e0 >> 3;
+          const Philox4 rnd = philox4x32_10(static_cast<uint32_t>(grp), static_cast<uint32_t>(grp >> 32), step,
+                                            p.salt, p.seed_lo, p.seed_hi);
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            v[g * 8 + q] = (rand16(rnd, q) >= p.drop_thr16) ? v[g * 8 + q] * p.drop_scale : 0.f;
+        } else {
+          // unaligned row start (N not a multiple of 8): one Philox call per element group it touches
+          for (int q = 0; q < 8; ++q) {
+            const unsigned long long e = e0 + q;
+            const unsigned long long grp = e >> 3;
+            const Philox4 rnd = philox4x32_10(static_cast<uint32_t>(grp), static_cast<uint32_t>(grp >> 32),
+                                              step, p.salt, p.seed_lo, p.seed_hi);
+            v[g * 8 + q] = (rand16(rnd, static_cast<int>(e & 7ull)) >= p.drop_thr16) ? v[g * 8 + q] * p.drop_scale
+                                                                                   : 0.f;
+          }
+        }
+      }
+    }
+    // backward mask of the previous layer's ReLU+dropout output
+    if (has_mask && row < p.M) {
+      const float* ms = p.mask_src + static_cast<size_t>(row) * p.ldm + col0;
+      if (col0 + 32 <= p.N && ((reinterpret_cast<uintptr_t>(ms) & 15u) == 0)) {
+        float4 mk[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) mk[q] = __ldg(reinterpret_cast<const float4*>(ms) + q);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          v[4 * q] = mk[q].x > 0.f ? v[4 * q] * p.mask_scale : 0.f;
+          v[4 * q + 1] = mk[q].y > 0.f ? v[4 * q + 1] * p.mask_scale : 0.f;
+          v[4 * q + 2] = mk[q].z > 0.f ? v[4 * q + 2] * p.mask_scale : 0.f;
+          v[4 * q + 3] = mk[q].w > 0.f ? v[4 * q + 3] * p.mask_scale : 0.f;
+        }
+      } else {
+#pragma unroll
+        for (int q = 0; q < 32; ++q)
+          if (col0 + q < p.N) v[q] = (__ldg(ms + q) > 0.f) ? v[q] * p.mask_scale : 0.f;
+      }
+    }
+    if (p.debug & 4) continue;
+    if (p.tma_store) {
+      // registers -> 128B-swizzled smem box -> one bulk tensor store per warp (clipped at the
+      // tensor edge by the TMA unit, full 128-byte lines on the wire)
+      uint8_t* box = stage_buf + (stores_issued & 1u) * 4096;
+      if (stores_issued >= 2) {
+        if (lane == 0) tma_store_wait_read<1>();  // the store issued two boxes ago has drained this one
+        __syncwarp();
+      }
+      uint8_t* rowp = box + lane * 128;
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        *reinterpret_cast<float4*>(rowp + ((q ^ (lane & 7)) << 4)) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_2d(tmOut, box, col0, m0 + wq * 32);
+        tma_store_commit();
+      }
+      ++stores_issued;
+    } else if (row < p.M) {
+      float* dst = p.out + static_cast<size_t>(row) * p.ldo + col0;
+      const int rem = n_cols_out - c * 32;
+      if (rem >= 32 && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0)) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          reinterpret_cast<float4*>(dst)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+      } else {
+#pragma unroll
+        for (int q = 0; q < 32; ++q)
+          if (q < rem) dst[q] = v[q];
+      }
+    }
+  }
 }
 
 template <bool A_MN, bool B_MN, int NSPLIT, int BK>
@@ -266,26 +407,18 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int et = threadIdx.x - (64 + SPLIT_THREADS);  // 0..127
     const int wq = warp & 3;                            // TMEM lane quarter this warp may read
     const int r_in_tile = wq * 32 + lane;
-    const bool has_drop = p.drop_thr16 != 0u;
-    const bool has_mask = p.mask_src != nullptr;
-    const bool relu = p.relu != 0;
     uint32_t step = p.step_imm;
-    if (has_drop && p.step_ptr != nullptr) step = *p.step_ptr;
+    if (p.drop_thr16 != 0u && p.step_ptr != nullptr) step = *p.step_ptr;
     uint8_t* stage_buf = staging + static_cast<size_t>(wq) * 8192;   // two 32x32 fp32 boxes per warp
     uint32_t stores_issued = 0;
-    uint32_t r[32];
     int j = 0;
     for (int u = blockIdx.x; u < total_units; u += gridDim.x, ++j) {
       const int tile = u % tiles, split = u / tiles;
       const int m0 = (tile % p.m_tiles) * BM, n0 = (tile / p.m_tiles) * p.bn;
       const int n_valid = min(p.bn, p.N - n0);
       const int umma_n = min(p.bn, (n_valid + 15) & ~15);
-      const int row = m0 + r_in_tile;
       const int buf = j & 1;
       const uint32_t taddr = tmem_base + static_cast<uint32_t>(buf) * MAX_BN + (static_cast<uint32_t>(wq * 32) << 16);
-      const int n_cols_out = min(p.bn, p.n_store - n0);  // columns to write (valid + zero padding)
-      const int n_chunks = (n_cols_out + 31) / 32;
-      const int acc_chunks = (umma_n + 31) / 32;         // chunks that hold MMA output
 
       // bias slice of this tile -> smem (zero beyond N); the barrier also fences the previous unit's reads
       named_bar_sync(1, EPI_THREADS);
@@ -296,128 +429,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);
       tcgen05_fence_after();
 
-      if (p.splits > 1) {
-        // split-K: park this split's partial tile in scratch; splitk_reduce_kernel sums the splits in
-        // order (deterministic) and applies the epilogue
-        float* my = p.scratch + (static_cast<size_t>(tile) * p.splits + split) * (BM * MAX_BN);
-        for (int c = 0; c < acc_chunks; ++c) {
-          tmem_ld_32x32(taddr + c * 32, r);
-          tmem_ld_wait();
-          float4* dst = reinterpret_cast<float4*>(my + (static_cast<size_t>(c) * BM + r_in_tile) * 32);
-#pragma unroll
-          for (int q = 0; q < 8; ++q)
-            dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
-                                 __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
-        }
-        tcgen05_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
-        continue;
-      }
-
-      for (int c = 0; c < n_chunks; ++c) {
-        float v[32];
-        if (c < acc_chunks) {
-          tmem_ld_32x32(taddr + c * 32, r);
-          tmem_ld_wait();
-        }
-        if (c == acc_chunks - 1 || (acc_chunks == 0 && c == 0)) {
-          // last TMEM read of this unit: hand the accumulator buffer back to the MMA warp
-          tcgen05_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
-        }
-#pragma unroll
-        for (int q = 0; q < 32; ++q) v[q] = (c < acc_chunks) ? __uint_as_float(r[q]) : 0.f;
-        // TMEM columns past the MMA's N were never written: force them (and their bias) to zero.
-        // Columns between N and umma_n hold exact zeros already (TMA zero-fills out-of-range B rows).
-        const int live = umma_n - c * 32;
-#pragma unroll
-        for (int q = 0; q < 32; ++q) {
-          float x = (q < live) ? v[q] + s_bias[c * 32 + q] : 0.f;
-          v[q] = relu ? fmaxf(x, 0.f) : x;
-        }
-        const int col0 = n0 + c * 32;
-        // dropout: element index e = row*N + col, 8 elements per Philox call, 16 bits each
-        if (has_drop && row < p.M) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const unsigned long long e0 =
-                static_cast<unsigned long long>(row) * static_cast<unsigned long long>(p.N) + (col0 + g * 8);
-            if ((e0 & 7ull) == 0ull) {
-              const unsigned long long grp = e0 >> 3;
-              const Philox4 rnd = philox4x32_10(static_cast<uint32_t>(grp), static_cast<uint32_t>(grp >> 32), step,
-                                                p.salt, p.seed_lo, p.seed_hi);
-#pragma unroll
-              for (int q = 0; q < 8; ++q)
-                v[g * 8 + q] = (rand16(rnd, q) >= p.drop_thr16) ? v[g * 8 + q] * p.drop_scale : 0.f;
-            } else {
-              // unaligned row start (N not a multiple of 8): one Philox call per element group it touches
-              for (int q = 0; q < 8; ++q) {
-                const unsigned long long e = e0 + q;
-                const unsigned long long grp = e >> 3;
-                const Philox4 rnd = philox4x32_10(static_cast<uint32_t>(grp), static_cast<uint32_t>(grp >> 32),
-                                                  step, p.salt, p.seed_lo, p.seed_hi);
-                v[g * 8 + q] = (rand16(rnd, static_cast<int>(e & 7ull)) >= p.drop_thr16) ? v[g * 8 + q] * p.drop_scale
-                                                                                       : 0.f;
-              }
-            }
-          }
-        }
-        // backward mask of the previous layer's ReLU+dropout output
-        if (has_mask && row < p.M) {
-          const float* ms = p.mask_src + static_cast<size_t>(row) * p.ldm + col0;
-          if (col0 + 32 <= p.N && ((reinterpret_cast<uintptr_t>(ms) & 15u) == 0)) {
-            float4 mk[8];
-#pragma unroll
-            for (int q = 0; q < 8; ++q) mk[q] = __ldg(reinterpret_cast<const float4*>(ms) + q);
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              v[4 * q] = mk[q].x > 0.f ? v[4 * q] * p.mask_scale : 0.f;
-              v[4 * q + 1] = mk[q].y > 0.f ? v[4 * q + 1] * p.mask_scale : 0.f;
-              v[4 * q + 2] = mk[q].z > 0.f ? v[4 * q + 2] * p.mask_scale : 0.f;
-              v[4 * q + 3] = mk[q].w > 0.f ? v[4 * q + 3] * p.mask_scale : 0.f;
-            }
-          } else {
-#pragma unroll
-            for (int q = 0; q < 32; ++q)
-              if (col0 + q < p.N) v[q] = (__ldg(ms + q) > 0.f) ? v[q] * p.mask_scale : 0.f;
-          }
-        }
-        if (p.debug & 4) continue;
-        if (p.tma_store) {
-          // registers -> 128B-swizzled smem box -> one bulk tensor store per warp (clipped at the
-          // tensor edge by the TMA unit, full 128-byte lines on the wire)
-          uint8_t* box = stage_buf + (stores_issued & 1u) * 4096;
-          if (stores_issued >= 2) {
-            if (lane == 0) tma_store_wait_read<1>();  // the store issued two boxes ago has drained this one
-            __syncwarp();
-          }
-          uint8_t* rowp = box + lane * 128;
-#pragma unroll
-          for (int q = 0; q < 8; ++q)
-            *reinterpret_cast<float4*>(rowp + ((q ^ (lane & 7)) << 4)) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            tma_store_2d(&tmOut, box, col0, m0 + wq * 32);
-            tma_store_commit();
-          }
-          ++stores_issued;
-        } else if (row < p.M) {
-          float* dst = p.out + static_cast<size_t>(row) * p.ldo + col0;
-          const int rem = n_cols_out - c * 32;
-          if (rem >= 32 && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0)) {
-#pragma unroll
-            for (int q = 0; q < 8; ++q)
-              reinterpret_cast<float4*>(dst)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-          } else {
-#pragma unroll
-            for (int q = 0; q < 32; ++q)
-              if (q < rem) dst[q] = v[q];
-          }
-        }
-      }
+      epilogue_unit(p, &tmOut, taddr, umma_n, tile, split, m0, n0, r_in_tile, lane, wq, s_bias, stage_buf, stores_issued, step,
+                    [&]() { if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]); });
     }
     if (p.tma_store && lane == 0) tma_store_wait_all();  // smem must outlive the bulk reads
   }
@@ -427,6 +440,232 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   if (stamps && threadIdx.x == 0) { stamps[5] = clock64(); stamps[6] = static_cast<long long>(global_timer_ns()); }
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ------------------------------------------------------------------------------------------------
+// CTA-pair variant of the 3xTF32 kernel (tcgen05 cta_group::2): a cluster of two CTAs on one TPC owns
+// a 256 x bn tile. Each CTA stages its own 128 rows of A and HALF of B, splits them locally, and the
+// leader's issuer thread runs M = 256 MMAs that read both CTAs' shared memory. Per SM and K block that
+// is 96 KB of shared-memory traffic instead of 144 KB, which lifts the 1-CTA kernel's smem-bandwidth
+// bound; L2 -> SM traffic for B halves as well.
+//   full[s]   per CTA   : own TMA bytes landed               (producer -> own splitters)
+//   ready[s]  leader    : 8 arrivals = 4 splitter warps x 2   (both CTAs' splitters -> leader issuer)
+//   empty[s]  per CTA   : tcgen05.commit multicast to both    (issuer -> both producers)
+//   tmem_full per CTA   : tcgen05.commit multicast to both    (issuer -> both epilogues)
+//   tmem_empty leader   : 8 arrivals                          (both epilogues -> issuer)
+template <bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                        const __grid_constant__ CUtensorMap tmOut, const GemmParams p) {
+  constexpr int BK = 16;
+  extern __shared__ uint8_t smem_dyn[];
+  __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
+  __shared__ __align__(8) uint64_t ready_bar[MAX_STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ uint32_t tmem_base_slot;
+  __shared__ float s_bias[MAX_BN];
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+
+  const uint32_t dyn_base = smem_u32(smem_dyn);
+  const uint32_t ring = (dyn_base + 1023u) & ~1023u;
+  uint8_t* ring_ptr = smem_dyn + (ring - dyn_base);
+  uint8_t* staging = ring_ptr + static_cast<size_t>(p.stages) * p.stage_bytes;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&ready_bar[s], 2 * (SPLIT_THREADS / 32));
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full_bar[b], 1);
+      mbar_init(&tmem_empty_bar[b], 2 * (EPI_THREADS / 32));
+    }
+    mbar_fence_init();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    if (p.tma_store) tma_prefetch_desc(&tmOut);
+  }
+  if (warp == 1) {
+    tmem_alloc_2cta(&tmem_base_slot, TMEM_COLS);
+    tmem_relinquish_2cta();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // the peer's barriers are initialised before anybody arrives on them remotely
+  tcgen05_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+
+  const int tiles2 = p.m_tiles2 * p.n_tiles;
+  const int total_units = tiles2 * p.splits;
+  const int half_bn = p.bn >> 1;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer (both CTAs)
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int u = pair; u < total_units; u += num_pairs) {
+        const int tile2 = u % tiles2, split = u / tiles2;
+        const int m0 = (tile2 % p.m_tiles2) * (2 * BM) + static_cast<int>(rank) * BM;
+        const int nb0 = (tile2 / p.m_tiles2) * p.bn + static_cast<int>(rank) * half_bn;
+        const int kb_begin = split * p.kb_per_split;
+        const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
+        for (int it = 0; it < n_iters; ++it) {
+          mbar_wait_cluster(&empty_bar[s], ph ^ 1u);
+          uint8_t* sa = ring_ptr + static_cast<size_t>(s) * p.stage_bytes;
+          uint8_t* sb = sa + p.a_bytes;
+          mbar_expect_tx(&full_bar[s], p.a_bytes + p.b_bytes);
+          const int k0 = (kb_begin + it) * BK;
+          if (!A_MN) {
+            tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
+          } else {
+#pragma unroll
+            for (int b = 0; b < BM / 32; ++b) tma_load_2d(sa + b * (128 * BK), &tmA, &full_bar[s], m0 + 32 * b, k0);
+          }
+          if (!B_MN) {
+            tma_load_2d(sb, &tmB, &full_bar[s], k0, nb0);
+          } else {
+            for (int b = 0; b < half_bn / 32; ++b) tma_load_2d(sb + b * (128 * BK), &tmB, &full_bar[s], nb0 + 32 * b, k0);
+          }
+          if (++s == p.stages) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA only)
+    if (lane == 0 && rank == 0) {
+      const uint32_t tail_off = p.a_bytes + p.b_bytes;
+      constexpr uint32_t kmajor_sbo = 8u * BK * 4u;
+      constexpr uint32_t mn_box = 128u * BK;
+      const uint32_t a_lbo = A_MN ? mn_box : 16u, b_lbo = B_MN ? mn_box : 16u;
+      const uint32_t a_sbo = A_MN ? 512u : kmajor_sbo, b_sbo = B_MN ? 512u : kmajor_sbo;
+      const uint32_t a_lt = A_MN ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW64;
+      const uint32_t b_lt = B_MN ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW64;
+      const uint32_t a_kstep = A_MN ? 1024u : 32u, b_kstep = B_MN ? 1024u : 32u;
+      const uint32_t idesc = umma_idesc(UMMA_TF32, A_MN, B_MN, static_cast<uint32_t>(p.bn), 256);
+      int s = 0;
+      uint32_t ph = 0;
+      int j = 0;
+      for (int u = pair; u < total_units; u += num_pairs, ++j) {
+        const int split = u / tiles2;
+        const int kb_begin = split * p.kb_per_split;
+        const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
+        const int buf = j & 1;
+        mbar_wait_cluster(&tmem_empty_bar[buf], ((j >> 1) & 1) ^ 1u);
+        tcgen05_fence_after();
+        const uint32_t tmem_acc = tmem_base + static_cast<uint32_t>(buf) * MAX_BN;
+        for (int it = 0; it < n_iters; ++it) {
+          mbar_wait_cluster(&ready_bar[s], ph);
+          tcgen05_fence_after();
+          const uint32_t sa = ring + static_cast<uint32_t>(s) * p.stage_bytes;
+          const uint32_t sb = sa + p.a_bytes;
+          const int k_left = p.K - (kb_begin + it) * BK;
+          const int ksteps = min(BK / UMMA_K, (k_left + UMMA_K - 1) / UMMA_K);
+          for (int k = 0; k < ksteps; ++k) {
+            const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, a_sbo, a_lt);
+            const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, b_sbo, b_lt);
+            const uint64_t da_t = umma_smem_desc(sa + tail_off + k * a_kstep, a_lbo, a_sbo, a_lt);
+            const uint64_t db_t = umma_smem_desc(sb + tail_off + k * b_kstep, b_lbo, b_sbo, b_lt);
+            const uint32_t acc = (it > 0 || k > 0) ? 1u : 0u;
+            umma_tf32_ss_2cta(tmem_acc, da_t, db, idesc, acc);
+            umma_tf32_ss_2cta(tmem_acc, da, db_t, idesc, 1u);
+            umma_tf32_ss_2cta(tmem_acc, da, db, idesc, 1u);
+          }
+          tcgen05_commit_2cta(&empty_bar[s], 0x3);        // both CTAs' slots are free once these MMAs have read them
+          if (++s == p.stages) { s = 0; ph ^= 1u; }
+        }
+        tcgen05_commit_2cta(&tmem_full_bar[buf], 0x3);    // both halves of the accumulator are complete
+      }
+    }
+    __syncwarp();
+  } else if (warp < 2 + SPLIT_THREADS / 32) {
+    // ------------------------------------------------------------------ splitters (both CTAs, own tiles)
+    const int st = threadIdx.x - 64;
+    const uint32_t raw_bytes = p.a_bytes + p.b_bytes;
+    const int nvec = static_cast<int>(raw_bytes >> 4);
+    int s = 0;
+    uint32_t ph = 0;
+    for (int u = pair; u < total_units; u += num_pairs) {
+      const int split = u / tiles2;
+      const int kb_begin = split * p.kb_per_split;
+      const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
+      for (int it = 0; it < n_iters; ++it) {
+        mbar_wait(&full_bar[s], ph);
+        const float4* raw = reinterpret_cast<const float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes);
+        float4* tail = reinterpret_cast<float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes + raw_bytes);
+        constexpr int SPLIT_ILP = 4;
+        for (int base = st; base < nvec; base += SPLIT_THREADS * SPLIT_ILP) {
+          float4 v[SPLIT_ILP];
+#pragma unroll
+          for (int q = 0; q < SPLIT_ILP; ++q) {
+            const int i = base + q * SPLIT_THREADS;
+            if (i < nvec) v[q] = raw[i];
+          }
+#pragma unroll
+          for (int q = 0; q < SPLIT_ILP; ++q) {
+            const int i = base + q * SPLIT_THREADS;
+            if (i < nvec) {
+              float4 t;
+              t.x = v[q].x - __uint_as_float(__float_as_uint(v[q].x) & 0xFFFFE000u);
+              t.y = v[q].y - __uint_as_float(__float_as_uint(v[q].y) & 0xFFFFE000u);
+              t.z = v[q].z - __uint_as_float(__float_as_uint(v[q].z) & 0xFFFFE000u);
+              t.w = v[q].w - __uint_as_float(__float_as_uint(v[q].w) & 0xFFFFE000u);
+              tail[i] = t;
+            }
+          }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&ready_bar[s], 0);   // the leader's issuer waits for all 8 splitter warps
+        if (++s == p.stages) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps (both CTAs, own 128 rows)
+    const int et = threadIdx.x - (64 + SPLIT_THREADS);
+    const int wq = warp & 3;
+    const int r_in_tile = wq * 32 + lane;
+    uint32_t step = p.step_imm;
+    if (p.drop_thr16 != 0u && p.step_ptr != nullptr) step = *p.step_ptr;
+    uint8_t* stage_buf = staging + static_cast<size_t>(wq) * 8192;
+    uint32_t stores_issued = 0;
+    int j = 0;
+    for (int u = pair; u < total_units; u += num_pairs, ++j) {
+      const int tile2 = u % tiles2, split = u / tiles2;
+      const int m_tile128 = (tile2 % p.m_tiles2) * 2 + static_cast<int>(rank);
+      const int n_tile = tile2 / p.m_tiles2;
+      const int m0 = m_tile128 * BM, n0 = n_tile * p.bn;
+      const int tile128 = m_tile128 < p.m_tiles ? n_tile * p.m_tiles + m_tile128 : -1;   // -1: rows entirely past M
+      const int buf = j & 1;
+      const uint32_t taddr = tmem_base + static_cast<uint32_t>(buf) * MAX_BN + (static_cast<uint32_t>(wq * 32) << 16);
+      named_bar_sync(1, EPI_THREADS);
+      for (int c = et; c < MAX_BN; c += EPI_THREADS)
+        s_bias[c] = (p.bias != nullptr && c < p.bn && n0 + c < p.N) ? __ldg(p.bias + n0 + c) : 0.f;
+      named_bar_sync(1, EPI_THREADS);
+      mbar_wait_cluster(&tmem_full_bar[buf], (j >> 1) & 1);
+      tcgen05_fence_after();
+      epilogue_unit(p, &tmOut, taddr, p.bn, tile128, split, m0, n0, r_in_tile, lane, wq, s_bias, stage_buf, stores_issued, step,
+                    [&]() { if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[buf], 0); });
+    }
+    if (p.tma_store && lane == 0) tma_store_wait_all();
+  }
+
+  // teardown: nobody may leave (or free TMEM) while the peer can still read this CTA's smem / arrive here
+  tcgen05_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) tmem_dealloc_2cta(tmem_base, TMEM_COLS);
 }
 
 // Sums the split-K partial tiles (in split order, so the result is reproducible) and writes the
@@ -514,6 +753,7 @@ static int make_map(CUtensorMap* map, const float* base, int inner, int outer, i
 }
 
 struct Plan {
+  int two_cta, m_tiles2;
   int bk;
   int bn, stages, splits, kb_per_split, num_kb, m_tiles, n_tiles;
   uint32_t a_bytes, b_bytes, stage_bytes;
@@ -534,7 +774,11 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
   if (!d) return fail(RTDC_ERR_ARG, "null descriptor");
   if (d->M <= 0 || d->N <= 0 || d->K <= 0) return fail(RTDC_ERR_ARG, "M, N, K must be positive (got %d, %d, %d)", d->M, d->N, d->K);
   if (d->precision != 1 && d->precision != 3) return fail(RTDC_ERR_ARG, "precision must be 1 (tf32) or 3 (3xTF32)");
-  const int gran = d->b_mn ? 32 : 16;
+  // CTA pairs (cta_group::2) for the fp32-accurate path when the tile grid is big enough to pair up
+  const char* env2 = getenv("RTDC_GEMM_2CTA");
+  const bool two_cta = d->precision == 3 && d->N >= 256 && d->M > BM && (env2 && env2[0] == '1');   // opt-in until validated
+  pl->two_cta = two_cta ? 1 : 0;
+  const int gran = two_cta ? (d->b_mn ? 64 : 32) : (d->b_mn ? 32 : 16);
   int bn = d->bn;
   if (bn == 0) {
     const int nt = ceil_div(d->N, MAX_BN);
@@ -544,13 +788,14 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
     return fail(RTDC_ERR_ARG, "bn must be a multiple of %d in [%d, %d] (got %d)", gran, gran, MAX_BN, bn);
   pl->bn = bn;
   pl->m_tiles = ceil_div(d->M, BM);
+  pl->m_tiles2 = ceil_div(d->M, 2 * BM);
   pl->n_tiles = ceil_div(d->N, bn);
   if (d->n_store > d->N && d->n_store > pl->n_tiles * bn)
     return fail(RTDC_ERR_ARG, "n_store (%d) reaches beyond the last N tile", d->n_store);
   pl->bk = d->precision == 3 ? 16 : 32;
   pl->num_kb = ceil_div(d->K, pl->bk);
   pl->a_bytes = BM * pl->bk * 4;
-  pl->b_bytes = static_cast<uint32_t>(bn) * pl->bk * 4;
+  pl->b_bytes = static_cast<uint32_t>(two_cta ? bn / 2 : bn) * pl->bk * 4;   // a CTA of a pair stages half of B
   pl->stage_bytes = (pl->a_bytes + pl->b_bytes) * (d->precision == 3 ? 2u : 1u);
   int stages = static_cast<int>((SMEM_LIMIT - STATIC_SMEM_RESERVE - 1024 - EPI_STAGING_BYTES) / pl->stage_bytes);
   if (stages > MAX_STAGES) stages = MAX_STAGES;
@@ -558,11 +803,11 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
   if (stages < 1) return fail(RTDC_ERR_LIMIT, "tile does not fit shared memory");
   pl->stages = stages;
   pl->smem = static_cast<size_t>(stages) * pl->stage_bytes + EPI_STAGING_BYTES + 1024;
-  const int tiles = pl->m_tiles * pl->n_tiles;
+  const int tiles = (two_cta ? pl->m_tiles2 : pl->m_tiles) * pl->n_tiles;   // schedulable tiles (pair tiles in 2-CTA mode)
   int splits = d->splits;
   if (splits == 0) {
     splits = 1;
-    const int sms = need_device ? num_sms() : 148;
+    const int sms = (need_device ? num_sms() : 148) / (two_cta ? 2 : 1);
     if (tiles * 2 <= sms && d->K >= 512 && d->drop_p <= 0.f && d->mask_src == nullptr) {
       splits = sms / tiles;
       const int max_by_k = d->K / 256;  // keep >= 256 K elements per split
@@ -583,6 +828,17 @@ static size_t scratch_bytes_for(const Plan& pl) {
   if (pl.splits <= 1) return 0;
   const size_t tiles = static_cast<size_t>(pl.m_tiles) * pl.n_tiles;
   return tiles * pl.splits * (static_cast<size_t>(BM) * MAX_BN * 4);
+}
+
+template <bool A_MN, bool B_MN>
+static int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const GemmParams& gp, const Plan& pl, cudaStream_t st) {
+  auto kern = gemm_tf32x3_2cta_kernel<A_MN, B_MN>;
+  RTDC_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT - STATIC_SMEM_RESERVE));
+  const int units = pl.m_tiles2 * pl.n_tiles * pl.splits;
+  const int pairs = units < num_sms() / 2 ? units : num_sms() / 2;   // persistent: one CTA pair per TPC
+  kern<<<2 * pairs, NUM_THREADS, pl.smem, st>>>(ta, tb, to, gp);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
 }
 
 template <bool A_MN, bool B_MN, int NSPLIT, int BK>
@@ -633,7 +889,7 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   if (!d->a_mn) rc = make_map(&ta, d->a, d->K, d->M, d->lda, pl.bk, BM, sw_k);
   else          rc = make_map(&ta, d->a, d->M, d->K, d->lda, 32, pl.bk, sw_mn);
   if (rc != RTDC_OK) return rc;
-  if (!d->b_mn) rc = make_map(&tb, d->b, d->K, d->N, d->ldb, pl.bk, pl.bn, sw_k);
+  if (!d->b_mn) rc = make_map(&tb, d->b, d->K, d->N, d->ldb, pl.bk, pl.two_cta ? pl.bn / 2 : pl.bn, sw_k);
   else          rc = make_map(&tb, d->b, d->N, d->K, d->ldb, 32, pl.bk, sw_mn);
   if (rc != RTDC_OK) return rc;
 
@@ -641,7 +897,7 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   memset(&gp, 0, sizeof(gp));
   gp.M = d->M; gp.N = d->N; gp.K = d->K;
   gp.bn = pl.bn; gp.stages = pl.stages; gp.splits = pl.splits; gp.kb_per_split = pl.kb_per_split; gp.num_kb = pl.num_kb;
-  gp.m_tiles = pl.m_tiles; gp.n_tiles = pl.n_tiles;
+  gp.m_tiles = pl.m_tiles; gp.n_tiles = pl.n_tiles; gp.m_tiles2 = pl.m_tiles2;
   gp.a_bytes = pl.a_bytes; gp.b_bytes = pl.b_bytes; gp.stage_bytes = pl.stage_bytes;
   gp.out = d->out; gp.ldo = d->ldo; gp.n_store = n_store;
   gp.bias = d->bias; gp.relu = d->relu;
@@ -688,6 +944,12 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
 
 static int dispatch(const rtdc_gemm_desc* d, bool three, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
                     const rtdc::GemmParams& gp, const rtdc::Plan& pl, cudaStream_t st) {
+  if (pl.two_cta) {
+    if (!d->a_mn && !d->b_mn) return launch_2cta<false, false>(ta, tb, to, gp, pl, st);
+    if (!d->a_mn && d->b_mn)  return launch_2cta<false, true>(ta, tb, to, gp, pl, st);
+    if (d->a_mn && !d->b_mn)  return launch_2cta<true, false>(ta, tb, to, gp, pl, st);
+    return launch_2cta<true, true>(ta, tb, to, gp, pl, st);
+  }
   if (!d->a_mn && !d->b_mn) return three ? launch<false, false, 3, 16>(ta, tb, to, gp, pl, st) : launch<false, false, 1, 32>(ta, tb, to, gp, pl, st);
   if (!d->a_mn && d->b_mn)  return three ? launch<false, true, 3, 16>(ta, tb, to, gp, pl, st)  : launch<false, true, 1, 32>(ta, tb, to, gp, pl, st);
   if (d->a_mn && !d->b_mn)  return three ? launch<true, false, 3, 16>(ta, tb, to, gp, pl, st)  : launch<true, false, 1, 32>(ta, tb, to, gp, pl, st);
