@@ -81,6 +81,20 @@ int rtdc_softmax_ce(const float* logits, int ldz, const int64_t* labels, int row
                     void* scratch, size_t scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Fused training "head": last Linear (K -> classes, classes = 10 or 16, K <= 512) + trailing ReLU +
+ * softmax cross-entropy + that layer's whole backward, in one pass over the hidden activations h
+ * [rows, ldh] (exact fp32 FFMA): writes loss (mean), dw [classes, K], db [classes] and
+ * dh[rows, lddh] = (dlogits . w) * (h > 0) * mask_scale, with dlogits = (softmax - onehot) * grad_scale
+ * masked by the logit ReLU. Replaces a skinny forward GEMM, the loss kernel, a skinny wgrad (+ split-K
+ * reduce), the bias column sum and a skinny dgrad.
+ * ref: my_ray_module.py:105-106 (Linear(512,10)+ReLU), :156 (loss), :159 (backward).
+ * scratch: rtdc_mlp_head_scratch_bytes bytes (per-block partials; no initialisation needed). */
+size_t rtdc_mlp_head_scratch_bytes(int rows, int K, int classes);
+int rtdc_mlp_head_train(const float* h, int ldh, const float* w, const float* bias, const int64_t* labels, int rows,
+                        int K, int classes, float grad_scale, float mask_scale, float* dh, int lddh, float* dw,
+                        float* db, float* loss, void* scratch, size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Column sums of a [rows, cols] fp32 matrix (bias gradients, K6): out[c] = sum_r x[r*ld + c].
  * Deterministic two-stage reduction; scratch: rtdc_colsum_scratch_bytes(rows, cols).
  */

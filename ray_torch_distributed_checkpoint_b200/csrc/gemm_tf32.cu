@@ -521,9 +521,10 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
         const int kb_begin = split * p.kb_per_split;
         const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
         for (int it = 0; it < n_iters; ++it) {
-          mbar_wait_cluster(&empty_bar[s], ph ^ 1u);
+          if (p.debug & 64) mbar_wait(&empty_bar[s], ph ^ 1u); else mbar_wait_cluster(&empty_bar[s], ph ^ 1u);
           uint8_t* sa = ring_ptr + static_cast<size_t>(s) * p.stage_bytes;
           uint8_t* sb = sa + p.a_bytes;
+          if (p.debug & 1) { mbar_arrive(&full_bar[s]); if (++s == p.stages) { s = 0; ph ^= 1u; } continue; }
           mbar_expect_tx(&full_bar[s], p.a_bytes + p.b_bytes);
           const int k0 = (kb_begin + it) * BK;
           if (!A_MN) {
@@ -562,17 +563,17 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
         const int kb_begin = split * p.kb_per_split;
         const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
         const int buf = j & 1;
-        mbar_wait_cluster(&tmem_empty_bar[buf], ((j >> 1) & 1) ^ 1u);
+        if (p.debug & 64) mbar_wait(&tmem_empty_bar[buf], ((j >> 1) & 1) ^ 1u); else mbar_wait_cluster(&tmem_empty_bar[buf], ((j >> 1) & 1) ^ 1u);
         tcgen05_fence_after();
         const uint32_t tmem_acc = tmem_base + static_cast<uint32_t>(buf) * MAX_BN;
         for (int it = 0; it < n_iters; ++it) {
-          mbar_wait_cluster(&ready_bar[s], ph);
+          if (p.debug & 64) mbar_wait(&ready_bar[s], ph); else mbar_wait_cluster(&ready_bar[s], ph);
           tcgen05_fence_after();
           const uint32_t sa = ring + static_cast<uint32_t>(s) * p.stage_bytes;
           const uint32_t sb = sa + p.a_bytes;
           const int k_left = p.K - (kb_begin + it) * BK;
           const int ksteps = min(BK / UMMA_K, (k_left + UMMA_K - 1) / UMMA_K);
-          for (int k = 0; k < ksteps; ++k) {
+          for (int k = 0; k < ((p.debug & 2) ? 0 : ksteps); ++k) {
             const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, a_sbo, a_lt);
             const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, b_sbo, b_lt);
             const uint64_t da_t = umma_smem_desc(sa + tail_off + k * a_kstep, a_lbo, a_sbo, a_lt);
@@ -605,7 +606,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
         const float4* raw = reinterpret_cast<const float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes);
         float4* tail = reinterpret_cast<float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes + raw_bytes);
         constexpr int SPLIT_ILP = 4;
-        for (int base = st; base < nvec; base += SPLIT_THREADS * SPLIT_ILP) {
+        for (int base = st; base < ((p.debug & 8) ? 0 : nvec); base += SPLIT_THREADS * SPLIT_ILP) {
           float4 v[SPLIT_ILP];
 #pragma unroll
           for (int q = 0; q < SPLIT_ILP; ++q) {
@@ -653,7 +654,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       for (int c = et; c < MAX_BN; c += EPI_THREADS)
         s_bias[c] = (p.bias != nullptr && c < p.bn && n0 + c < p.N) ? __ldg(p.bias + n0 + c) : 0.f;
       named_bar_sync(1, EPI_THREADS);
-      mbar_wait_cluster(&tmem_full_bar[buf], (j >> 1) & 1);
+      if (p.debug & 64) mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1); else mbar_wait_cluster(&tmem_full_bar[buf], (j >> 1) & 1);
       tcgen05_fence_after();
       epilogue_unit(p, &tmOut, taddr, p.bn, tile128, split, m0, n0, r_in_tile, lane, wq, s_bias, stage_buf, stores_issued, step,
                     [&]() { if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[buf], 0); });

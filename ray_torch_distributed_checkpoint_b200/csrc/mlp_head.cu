@@ -1,0 +1,313 @@
+// Fused "head" of the reference MLP for training: the last Linear (hidden -> classes, classes <= 16),
+// its trailing ReLU, the softmax cross-entropy loss and ALL of that layer's backward in one pass over
+// the hidden activations (K3 + K4 + K5 + the layer-3 part of K6 in SURVEY.md §2.5; reference:
+// my_ray_module.py:105-106 forward, :156 loss, :159 backward).
+//
+// Why a dedicated kernel: with 10 output classes these ops are 1.3 % of the step's FLOPs but, run as
+// three skinny tensor-core GEMMs + a loss kernel + reductions, they were 16 % of its time — each of them
+// re-reads the 39 MB activation matrix and pays a full pipeline prologue for almost no math. Here a
+// block loads a 64-row tile of H once into shared memory and produces, in exact fp32 FFMA arithmetic:
+//   z = relu(H W^T + b)            (never written out)
+//   loss_i, dz = (softmax(z) - onehot) * grad_scale * 1[z > 0]
+//   dH = (dz W) * 1[H > 0] * mask_scale      -> global (the only large write)
+//   dW += dz^T H,  db += sum_rows dz          -> per-block partials, summed in block order by head_reduce
+#include "common.h"
+#include "../../include/rtdc_b200.h"
+
+namespace rtdc {
+
+constexpr int HD_ROWS = 64;       // rows of H per tile
+constexpr int HD_THREADS = 256;
+constexpr int HD_MAXK = 512;      // hidden width limit (smem tile 64 x 512 fp32 = 128 KB)
+constexpr int HD_PAD = 4;         // row padding (floats) -> conflict-free 128-bit accesses across rows
+constexpr int HD_DZ_LD = 16;      // dz rows padded to 16 floats
+
+struct HeadParams {
+  const float* h; int ldh;
+  const float* w;                 // [C, K] row-major
+  const float* bias;              // [C]
+  const long long* labels;
+  int rows, K;
+  float grad_scale, mask_scale;
+  float* dh; int lddh;
+  float* dw_partial;              // [grid][C][K]
+  float* db_partial;              // [grid][16]
+  float* loss_partial;            // [grid]
+};
+
+template <int C>
+__global__ void __launch_bounds__(HD_THREADS, 1)
+mlp_head_train_kernel(const HeadParams p) {
+  extern __shared__ __align__(16) float smem[];
+  const int K = p.K, K4 = K >> 2, LD = K + HD_PAD;
+  float* sh = smem;                        // [HD_ROWS][LD]
+  float* sw = sh + HD_ROWS * LD;           // [C][LD]
+  float* sdz = sw + C * LD;                // [HD_ROWS][HD_DZ_LD]
+  float* sb = sdz + HD_ROWS * HD_DZ_LD;    // [16]
+  __shared__ float s_red[HD_THREADS / 32];
+
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  // weights + bias -> smem once per block
+  for (int i = t; i < C * K4; i += HD_THREADS) {
+    const int c = i / K4, k4 = i - c * K4;
+    *reinterpret_cast<float4*>(sw + c * LD + 4 * k4) = __ldg(reinterpret_cast<const float4*>(p.w + static_cast<size_t>(c) * K) + k4);
+  }
+  if (t < 16) sb[t] = (t < C && p.bias != nullptr) ? __ldg(p.bias + t) : 0.f;
+
+  // persistent accumulators
+  constexpr int CH = (C + 1) / 2;          // classes per thread group in the dW phase
+  float4 dw_acc[CH];
+#pragma unroll
+  for (int c = 0; c < CH; ++c) dw_acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+  float db_acc = 0.f;                      // thread t < C owns class t
+  float loss_acc = 0.f;
+
+  const int tiles = (p.rows + HD_ROWS - 1) / HD_ROWS;
+  for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const int row0 = tile * HD_ROWS;
+    __syncthreads();                       // previous tile's readers are done with sh / sdz
+    // ---- A: H tile -> smem (coalesced 128-bit loads, 8 in flight per thread)
+    {
+      const int total = HD_ROWS * K4;
+      for (int base = t; base < total; base += HD_THREADS * 8) {
+        float4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int i = base + u * HD_THREADS;
+          if (i < total) {
+            const int r = i / K4, k4 = i - r * K4;
+            v[u] = (row0 + r < p.rows) ? __ldg(reinterpret_cast<const float4*>(p.h + static_cast<size_t>(row0 + r) * p.ldh) + k4)
+                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int i = base + u * HD_THREADS;
+          if (i < total) {
+            const int r = i / K4, k4 = i - r * K4;
+            *reinterpret_cast<float4*>(sh + r * LD + 4 * k4) = v[u];
+          }
+        }
+      }
+    }
+    __syncthreads();
+
+    // ---- B: logits for two rows per thread (8 threads share a row pair and stride over K), then CE
+    {
+      const int g = t & 7, rp = t >> 3;    // rp in 0..31: rows rp and rp + 32
+      float a0[C], a1[C];
+#pragma unroll
+      for (int c = 0; c < C; ++c) { a0[c] = 0.f; a1[c] = 0.f; }
+      const float* h0 = sh + rp * LD;
+      const float* h1 = sh + (rp + 32) * LD;
+      for (int k4 = g; k4 < K4; k4 += 8) {
+        const float4 x0 = *reinterpret_cast<const float4*>(h0 + 4 * k4);
+        const float4 x1 = *reinterpret_cast<const float4*>(h1 + 4 * k4);
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const float4 wv = *reinterpret_cast<const float4*>(sw + c * LD + 4 * k4);
+          a0[c] = fmaf(x0.x, wv.x, fmaf(x0.y, wv.y, fmaf(x0.z, wv.z, fmaf(x0.w, wv.w, a0[c]))));
+          a1[c] = fmaf(x1.x, wv.x, fmaf(x1.y, wv.y, fmaf(x1.z, wv.z, fmaf(x1.w, wv.w, a1[c]))));
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+          a0[c] += __shfl_xor_sync(0xffffffffu, a0[c], o);
+          a1[c] += __shfl_xor_sync(0xffffffffu, a1[c], o);
+        }
+      }
+      if (g < 2) {                         // g == 0 finishes row rp, g == 1 finishes row rp + 32
+        const int r = rp + 32 * g;
+        const int row = row0 + r;
+        float z[C];
+        float mx = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          z[c] = fmaxf((g == 0 ? a0[c] : a1[c]) + sb[c], 0.f);
+          mx = fmaxf(mx, z[c]);
+        }
+        float sum = 0.f, e[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) { e[c] = __expf(z[c] - mx); sum += e[c]; }
+        float* dzr = sdz + r * HD_DZ_LD;
+        if (row < p.rows) {
+          const long long y = p.labels[row];
+          float zy = 0.f;
+          const float inv = p.grad_scale / sum;
+#pragma unroll
+          for (int c = 0; c < C; ++c) {
+            if (c == y) zy = z[c];
+            const float d = e[c] * inv - ((c == y) ? p.grad_scale : 0.f);
+            dzr[c] = (z[c] > 0.f) ? d : 0.f;
+          }
+          loss_acc += (mx + __logf(sum)) - zy;
+        } else {
+#pragma unroll
+          for (int c = 0; c < C; ++c) dzr[c] = 0.f;
+        }
+#pragma unroll
+        for (int c = C; c < HD_DZ_LD; ++c) dzr[c] = 0.f;
+      }
+    }
+    __syncthreads();
+
+    // ---- db: class t sums its column of dz
+    if (t < C) {
+      float sacc = 0.f;
+      for (int r = 0; r < HD_ROWS; ++r) sacc += sdz[r * HD_DZ_LD + t];
+      db_acc += sacc;
+    }
+
+    const int k4 = t & 127, grp = t >> 7;  // two groups of 128 threads; thread owns columns 4*k4..4*k4+3
+    if (k4 < K4) {
+      // ---- C: dH = (dz W) masked by H > 0, rows grp*32 .. grp*32+31
+      {
+        float4 wr[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) wr[c] = *reinterpret_cast<const float4*>(sw + c * LD + 4 * k4);
+        for (int r = grp * 32; r < grp * 32 + 32; ++r) {
+          const int row = row0 + r;
+          if (row >= p.rows) break;
+          float d[HD_DZ_LD];
+#pragma unroll
+          for (int q = 0; q < (C + 3) / 4; ++q) {
+            const float4 tq = *reinterpret_cast<const float4*>(sdz + r * HD_DZ_LD + 4 * q);
+            d[4 * q] = tq.x; d[4 * q + 1] = tq.y; d[4 * q + 2] = tq.z; d[4 * q + 3] = tq.w;
+          }
+          const float4 hv = *reinterpret_cast<const float4*>(sh + r * LD + 4 * k4);
+          float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int c = 0; c < C; ++c) {
+            o.x = fmaf(d[c], wr[c].x, o.x); o.y = fmaf(d[c], wr[c].y, o.y);
+            o.z = fmaf(d[c], wr[c].z, o.z); o.w = fmaf(d[c], wr[c].w, o.w);
+          }
+          o.x = hv.x > 0.f ? o.x * p.mask_scale : 0.f;
+          o.y = hv.y > 0.f ? o.y * p.mask_scale : 0.f;
+          o.z = hv.z > 0.f ? o.z * p.mask_scale : 0.f;
+          o.w = hv.w > 0.f ? o.w * p.mask_scale : 0.f;
+          *reinterpret_cast<float4*>(p.dh + static_cast<size_t>(row) * p.lddh + 4 * k4) = o;
+        }
+      }
+      // ---- D: dW[c][k] += sum_r dz[r][c] * H[r][k], classes grp*CH .. grp*CH+CH-1
+      for (int r = 0; r < HD_ROWS; ++r) {
+        const float4 hv = *reinterpret_cast<const float4*>(sh + r * LD + 4 * k4);
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+          const int cc = grp * CH + c;
+          const float d = cc < C ? sdz[r * HD_DZ_LD + cc] : 0.f;
+          dw_acc[c].x = fmaf(d, hv.x, dw_acc[c].x); dw_acc[c].y = fmaf(d, hv.y, dw_acc[c].y);
+          dw_acc[c].z = fmaf(d, hv.z, dw_acc[c].z); dw_acc[c].w = fmaf(d, hv.w, dw_acc[c].w);
+        }
+      }
+    }
+  }
+
+  // ---- block partials
+  {
+    const int k4 = t & 127, grp = t >> 7;
+    if (k4 < K4) {
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        const int cc = grp * CH + c;
+        if (cc < C)
+          *reinterpret_cast<float4*>(p.dw_partial + (static_cast<size_t>(blockIdx.x) * C + cc) * K + 4 * k4) = dw_acc[c];
+      }
+    }
+    if (t < 16) p.db_partial[blockIdx.x * 16 + t] = t < C ? db_acc : 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) loss_acc += __shfl_xor_sync(0xffffffffu, loss_acc, o);
+    if (lane == 0) s_red[warp] = loss_acc;
+    __syncthreads();
+    if (t == 0) {
+      float tot = 0.f;
+      for (int wv = 0; wv < HD_THREADS / 32; ++wv) tot += s_red[wv];
+      p.loss_partial[blockIdx.x] = tot;
+    }
+  }
+}
+
+// Sums the per-block partials in block order (reproducible): one thread per dW element, plus db and loss.
+__global__ void __launch_bounds__(256)
+mlp_head_reduce_kernel(const float* __restrict__ dw_partial, const float* __restrict__ db_partial,
+                       const float* __restrict__ loss_partial, int nblocks, int CK, int C, int rows, float* __restrict__ dw,
+                       float* __restrict__ db, float* __restrict__ loss) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < CK) {
+    float acc = 0.f;
+    for (int b0 = 0; b0 < nblocks; b0 += 8) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = (b0 + u < nblocks) ? __ldcg(dw_partial + static_cast<size_t>(b0 + u) * CK + i) : 0.f;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc += v[u];
+    }
+    dw[i] = acc;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < 32) {
+    if (threadIdx.x < C) {
+      float acc = 0.f;
+      for (int b = 0; b < nblocks; ++b) acc += __ldcg(db_partial + b * 16 + threadIdx.x);
+      db[threadIdx.x] = acc;
+    }
+    if (threadIdx.x == 31) {
+      float acc = 0.f;
+      for (int b = 0; b < nblocks; ++b) acc += __ldcg(loss_partial + b);
+      *loss = acc / static_cast<float>(rows);
+    }
+  }
+}
+
+static size_t head_smem_bytes(int C, int K) {
+  return (static_cast<size_t>(HD_ROWS + C) * (K + HD_PAD) + HD_ROWS * HD_DZ_LD + 16) * sizeof(float);
+}
+
+}  // namespace rtdc
+
+using namespace rtdc;
+
+static int head_grid(int rows) {
+  const int tiles = (rows + HD_ROWS - 1) / HD_ROWS;
+  return tiles < 148 ? tiles : 148;
+}
+
+RTDC_API size_t rtdc_mlp_head_scratch_bytes(int rows, int K, int classes) {
+  const size_t g = static_cast<size_t>(head_grid(rows));
+  return g * (static_cast<size_t>(classes) * K + 16 + 4) * sizeof(float) + 256;
+}
+
+RTDC_API int rtdc_mlp_head_train(const float* h, int ldh, const float* w, const float* bias, const int64_t* labels, int rows,
+                                 int K, int classes, float grad_scale, float mask_scale, float* dh, int lddh, float* dw,
+                                 float* db, float* loss, void* scratch, size_t scratch_bytes, void* stream) {
+  if (!h || !w || !labels || !dh || !dw || !db || !loss) return fail(RTDC_ERR_ARG, "mlp_head_train: null pointer");
+  if (rows <= 0 || K <= 0 || K > HD_MAXK || (K & 3) || (ldh & 3) || (lddh & 3))
+    return fail(RTDC_ERR_LIMIT, "mlp_head_train: hidden width must be a multiple of 4 and <= %d, row pitches multiples of 4 (K=%d)", HD_MAXK, K);
+  if (classes != 10 && classes != 16) return fail(RTDC_ERR_LIMIT, "mlp_head_train is built for 10 or 16 classes (got %d)", classes);
+  if ((reinterpret_cast<uintptr_t>(h) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(dh)) & 15u)
+    return fail(RTDC_ERR_ARG, "mlp_head_train: h, w and dh must be 16-byte aligned");
+  const size_t need = rtdc_mlp_head_scratch_bytes(rows, K, classes);
+  if (!scratch || scratch_bytes < need) return fail(RTDC_ERR_ARG, "mlp_head_train needs %zu bytes of scratch (got %zu)", need, scratch_bytes);
+  const int grid = head_grid(rows);
+  HeadParams p;
+  p.h = h; p.ldh = ldh; p.w = w; p.bias = bias; p.labels = reinterpret_cast<const long long*>(labels);
+  p.rows = rows; p.K = K; p.grad_scale = grad_scale; p.mask_scale = mask_scale; p.dh = dh; p.lddh = lddh;
+  float* base = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(scratch) + 255) & ~static_cast<uintptr_t>(255));
+  p.dw_partial = base;
+  p.db_partial = base + static_cast<size_t>(grid) * classes * K;
+  p.loss_partial = p.db_partial + static_cast<size_t>(grid) * 16;
+  const size_t smem = head_smem_bytes(classes, K);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (classes == 10) {
+    RTDC_CUDA_CHECK(cudaFuncSetAttribute(mlp_head_train_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    mlp_head_train_kernel<10><<<grid, HD_THREADS, smem, st>>>(p);
+  } else {
+    RTDC_CUDA_CHECK(cudaFuncSetAttribute(mlp_head_train_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    mlp_head_train_kernel<16><<<grid, HD_THREADS, smem, st>>>(p);
+  }
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  const int CK = classes * K;
+  mlp_head_reduce_kernel<<<(CK + 255) / 256, 256, 0, st>>>(p.dw_partial, p.db_partial, p.loss_partial, grid, CK, classes, rows, dw, db, loss);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}

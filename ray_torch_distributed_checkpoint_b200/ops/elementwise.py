@@ -50,6 +50,26 @@ def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor, *, classes
     return loss_out
 
 
+def mlp_head_train(h: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], labels: torch.Tensor, *,
+                   dh: torch.Tensor, dw: torch.Tensor, db: torch.Tensor, loss: Optional[torch.Tensor] = None,
+                   grad_scale: Optional[float] = None, mask_scale: float = 1.0, stream=None) -> torch.Tensor:
+    """Fused last layer for training: ``z = relu(h @ weight.T + bias)``, mean cross-entropy, and the layer's
+    backward (``dw``, ``db``, ``dh = (dz @ weight) * (h > 0) * mask_scale``) in one pass over ``h``.
+    ``weight`` is ``[classes, K]`` with 10 or 16 classes and ``K <= 512``."""
+    rows, K = h.shape
+    classes = weight.shape[0]
+    if loss is None:
+        loss = torch.empty((), dtype=torch.float32, device=h.device)
+    lib = _lib.load()
+    ws = scratch_for("head", lib.rtdc_mlp_head_scratch_bytes(rows, K, classes), h.device, stream)
+    gs = (1.0 / rows) if grad_scale is None else grad_scale
+    _lib.check(lib.rtdc_mlp_head_train(h.data_ptr(), h.stride(0), weight.data_ptr(), bias.data_ptr() if bias is not None else None,
+                                       labels.data_ptr(), rows, K, classes, gs, mask_scale, dh.data_ptr(), dh.stride(0),
+                                       dw.data_ptr(), db.data_ptr(), loss.data_ptr(), ws.data_ptr(), ws.numel(),
+                                       _lib.stream_ptr(stream)))
+    return loss
+
+
 def colsum(x: torch.Tensor, *, cols: Optional[int] = None, out: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
     """``out[c] = sum_r x[r, c]`` for the first ``cols`` columns (bias gradient)."""
     if x.dtype != torch.float32 or not x.is_cuda or x.dim() != 2 or x.stride(1) != 1:

@@ -32,7 +32,7 @@ class MLPTrainEngine:
     def __init__(self, model: Optional[NeuralNetwork] = None, *, batch_size: int, lr: float = 1e-3, momentum: float = 0.9,
                  weight_decay: float = 0.0, device=None, seed: int = 0x5EED, precision: int = ops.PRECISION_FP32,
                  use_graph: bool = True, process_group=None, distributed: Optional[bool] = None, algo: str = "auto",
-                 input_mean: float = 0.5, input_std: float = 0.5):
+                 input_mean: float = 0.5, input_std: float = 0.5, fused_head: bool = True):
         self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
         if self.device.type == "cuda" and self.device.index is None:
             self.device = torch.device("cuda", torch.cuda.current_device())
@@ -112,6 +112,8 @@ class MLPTrainEngine:
         self._warm: Dict[str, int] = {}
         self.stream = torch.cuda.Stream(dev)
         self.kernel_launches_per_step = {}
+        # one-pass fused last layer (forward + loss + backward) when its shape limits allow it
+        self.fused_head = fused_head and self.d_h <= 512 and self.d_h % 4 == 0 and self.d_out in (10, 16)
 
     # ------------------------------------------------------------------------------------------ helpers
     def _view(self, arena: torch.Tensor, name: str) -> torch.Tensor:
@@ -139,7 +141,7 @@ class MLPTrainEngine:
                              stream=self.comm_stream)
 
     # ------------------------------------------------------------------------------------------ the step
-    def _forward(self, s, train: bool, from_u8: bool):
+    def _forward(self, s, train: bool, from_u8: bool, with_logits: bool = True):
         n = 0
         p = self.p_drop if train else 0.0
         kw = dict(seed=self.seed, step_tensor=self.step_counter, precision=self.precision, stream=s)
@@ -147,19 +149,25 @@ class MLPTrainEngine:
             ops.u8_normalize(self.x_u8, mean=self.mean, std=self.std, out=self.x, stream=s); n += 1
         ops.linear_forward(self.x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, **kw); n += 1
         ops.linear_forward(self.h1, self.W[1], self.b[1], relu=True, drop_p=p, salt=2, out=self.h2, **kw); n += 1
-        ops.linear_forward(self.h2, self.W[2], self.b[2], relu=True, out=self.z, n_store=_LOGIT_LD, **kw); n += 1
+        if with_logits:
+            ops.linear_forward(self.h2, self.W[2], self.b[2], relu=True, out=self.z, n_store=_LOGIT_LD, **kw); n += 1
         return n
 
     def _enqueue_train_step(self, s: torch.cuda.Stream, from_u8: bool) -> int:
         B, prec = self.B, self.precision
         inv_keep = 1.0 / (1.0 - self.p_drop) if self.p_drop > 0 else 1.0
-        n = self._forward(s, True, from_u8)
-        ops.softmax_cross_entropy(self.z, self.y, classes=self.d_out, dlogits=self.dz, grad_scale=1.0 / B, relu_mask=True,
-                                  loss_out=self.loss, dbias_out=self.db[2], stream=s); n += 1   # also emits db3
-        # layer 3
-        ops.linear_wgrad(self.dz, self.h2, N_out=self.d_out, out=self.dW[2], precision=prec, stream=s); n += 2
-        ops.linear_dgrad(self.dz, self.W[2], N_out=self.d_out, mask_src=self.h2, mask_scale=inv_keep, out=self.dh2,
-                         precision=prec, stream=s); n += 1
+        fused_head = self.fused_head
+        n = self._forward(s, True, from_u8, with_logits=not fused_head)
+        if fused_head:
+            # layer 3 forward + loss + layer 3 backward in one pass over h2 (exact fp32 on the CUDA cores)
+            ops.mlp_head_train(self.h2, self.W[2], self.b[2], self.y, dh=self.dh2, dw=self.dW[2], db=self.db[2], loss=self.loss,
+                               grad_scale=1.0 / B, mask_scale=inv_keep, stream=s); n += 2
+        else:
+            ops.softmax_cross_entropy(self.z, self.y, classes=self.d_out, dlogits=self.dz, grad_scale=1.0 / B, relu_mask=True,
+                                      loss_out=self.loss, dbias_out=self.db[2], stream=s); n += 1   # also emits db3
+            ops.linear_wgrad(self.dz, self.h2, N_out=self.d_out, out=self.dW[2], precision=prec, stream=s); n += 2
+            ops.linear_dgrad(self.dz, self.W[2], N_out=self.d_out, mask_src=self.h2, mask_scale=inv_keep, out=self.dh2,
+                             precision=prec, stream=s); n += 1
         # layer 2
         ops.linear_wgrad(self.dh2, self.h1, out=self.dW[1], precision=prec, stream=s); n += 2
         ops.colsum(self.dh2, out=self.db[1], stream=s); n += 1

@@ -106,3 +106,25 @@ def test_fused_adam_matches_torch(decoupled):
         opt.step()
         ops.adam_step(p, g, m, v, st)
         assert torch.allclose(p, ref_p.detach(), rtol=2e-5, atol=2e-6), f"step {i}"
+
+
+@pytest.mark.parametrize("rows,classes", [(1000, 10), (64, 10), (4133, 16), (18944, 10)])
+def test_fused_mlp_head_matches_autograd(rows, classes):
+    ops = _ops()
+    K, p = 512, 0.25
+    g = torch.Generator(device="cuda").manual_seed(rows + classes)
+    h = torch.relu(torch.randn(rows, K, device="cuda", generator=g)) * (torch.rand(rows, K, device="cuda", generator=g) > p)
+    w = torch.randn(classes, K, device="cuda", generator=g) * 0.05
+    b = torch.randn(classes, device="cuda", generator=g) * 0.1
+    y = torch.randint(0, classes, (rows,), device="cuda", generator=g)
+    dh = torch.full((rows, K), 3.0, device="cuda"); dw = torch.empty(classes, K, device="cuda"); db = torch.empty(classes, device="cuda")
+    for _ in range(2):
+        loss = ops.mlp_head_train(h, w, b, y, dh=dh, dw=dw, db=db, mask_scale=1 / (1 - p))
+    hr = h.double().requires_grad_(True); wr = w.double().requires_grad_(True); br = b.double().requires_grad_(True)
+    ref = F.cross_entropy(torch.relu(hr @ wr.T + br), y)
+    ref.backward()
+    assert abs(loss.item() - ref.item()) < 1e-5 * max(1.0, abs(ref.item()))
+    ref_dh = hr.grad * (h > 0) / (1 - p)
+    assert torch.allclose(dh.double(), ref_dh, rtol=1e-4, atol=1e-9)
+    assert (dw.double() - wr.grad).norm() / wr.grad.norm() < 1e-5
+    assert (db.double() - br.grad).norm() / br.grad.norm() < 1e-5

@@ -18,7 +18,7 @@ def t(fn, n=10):
         g.replay(); s.synchronize()
         a.record(s); g.replay(); b.record(s); s.synchronize()
     return a.elapsed_time(b) / n * 1000
-for dbg in (0, 8, 2, 10, 1, 3, 11):
+for dbg in [int(v) for v in (sys.argv[1:] or ['0', '8', '2', '10', '1', '3', '11'])]:
     os.environ["RTDC_GEMM_DEBUG"] = str(dbg)
     us = t(lambda: ops.gemm(x, w1, out, bias=b1, relu=True, precision=3))
     print(f"fwd1 prec=3 B={B} debug={dbg}: {us:.1f} us", flush=True)
