@@ -204,11 +204,14 @@ colsum_kernel(const float* __restrict__ x, int ld, int rows, int cols, float* __
   constexpr int WARPS = CS_THREADS / 32;
   int r = r_begin + warp;
   if (vec) {
-    for (; r + (ROWS_ILP - 1) * WARPS < r_end; r += ROWS_ILP * WARPS) {
+    // every batch (the last, partial one included) keeps ROWS_ILP independent loads in flight
+    for (; r < r_end; r += ROWS_ILP * WARPS) {
       float4 t[ROWS_ILP];
 #pragma unroll
-      for (int u = 0; u < ROWS_ILP; ++u)
-        t[u] = __ldg(reinterpret_cast<const float4*>(x + static_cast<size_t>(r + u * WARPS) * ld + c0));
+      for (int u = 0; u < ROWS_ILP; ++u) {
+        const int rr = r + u * WARPS;
+        t[u] = rr < r_end ? __ldg(reinterpret_cast<const float4*>(x + static_cast<size_t>(rr) * ld + c0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
 #pragma unroll
       for (int u = 0; u < ROWS_ILP; ++u) { acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w; }
     }

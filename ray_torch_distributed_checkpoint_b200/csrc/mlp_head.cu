@@ -17,7 +17,7 @@
 namespace rtdc {
 
 constexpr int HD_ROWS = 64;       // rows of H per tile
-constexpr int HD_THREADS = 256;
+constexpr int HD_THREADS = 512;     // 16 warps: one block per SM (157 KB of smem), so latency hiding has to come from warps
 constexpr int HD_MAXK = 512;      // hidden width limit (smem tile 64 x 512 fp32 = 128 KB)
 constexpr int HD_PAD = 4;         // row padding (floats) -> conflict-free 128-bit accesses across rows
 constexpr int HD_DZ_LD = 16;      // dz rows padded to 16 floats
@@ -55,7 +55,7 @@ mlp_head_train_kernel(const HeadParams p) {
   if (t < 16) sb[t] = (t < C && p.bias != nullptr) ? __ldg(p.bias + t) : 0.f;
 
   // persistent accumulators
-  constexpr int CH = (C + 1) / 2;          // classes per thread group in the dW phase
+  constexpr int CH = (C + 3) / 4;          // classes per thread group in the dW phase (four groups)
   float4 dw_acc[CH];
 #pragma unroll
   for (int c = 0; c < CH; ++c) dw_acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -66,41 +66,33 @@ mlp_head_train_kernel(const HeadParams p) {
   for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
     const int row0 = tile * HD_ROWS;
     __syncthreads();                       // previous tile's readers are done with sh / sdz
-    // ---- A: H tile -> smem (coalesced 128-bit loads, 8 in flight per thread)
+    // ---- A: H tile -> smem with cp.async (16 bytes each, every load of the tile in flight at once)
     {
       const int total = HD_ROWS * K4;
-      for (int base = t; base < total; base += HD_THREADS * 8) {
-        float4 v[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int i = base + u * HD_THREADS;
-          if (i < total) {
-            const int r = i / K4, k4 = i - r * K4;
-            v[u] = (row0 + r < p.rows) ? __ldg(reinterpret_cast<const float4*>(p.h + static_cast<size_t>(row0 + r) * p.ldh) + k4)
-                                       : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int i = base + u * HD_THREADS;
-          if (i < total) {
-            const int r = i / K4, k4 = i - r * K4;
-            *reinterpret_cast<float4*>(sh + r * LD + 4 * k4) = v[u];
-          }
+      for (int i = t; i < total; i += HD_THREADS) {
+        const int r = i / K4, k4 = i - r * K4;
+        float* dst = sh + r * LD + 4 * k4;
+        if (row0 + r < p.rows) {
+          const float* src = p.h + static_cast<size_t>(row0 + r) * p.ldh + 4 * k4;
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(dst))), "l"(src) : "memory");
+        } else {
+          *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
       }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
     __syncthreads();
 
-    // ---- B: logits for two rows per thread (8 threads share a row pair and stride over K), then CE
+    // ---- B: logits for two rows per thread (16 threads share a row pair and stride over K), then CE
     {
-      const int g = t & 7, rp = t >> 3;    // rp in 0..31: rows rp and rp + 32
+      const int g = t & 15, rp = t >> 4;   // rp in 0..31: rows rp and rp + 32
       float a0[C], a1[C];
 #pragma unroll
       for (int c = 0; c < C; ++c) { a0[c] = 0.f; a1[c] = 0.f; }
       const float* h0 = sh + rp * LD;
       const float* h1 = sh + (rp + 32) * LD;
-      for (int k4 = g; k4 < K4; k4 += 8) {
+      for (int k4 = g; k4 < K4; k4 += 16) {
         const float4 x0 = *reinterpret_cast<const float4*>(h0 + 4 * k4);
         const float4 x1 = *reinterpret_cast<const float4*>(h1 + 4 * k4);
 #pragma unroll
@@ -113,7 +105,7 @@ mlp_head_train_kernel(const HeadParams p) {
 #pragma unroll
       for (int c = 0; c < C; ++c) {
 #pragma unroll
-        for (int o = 1; o < 8; o <<= 1) {
+        for (int o = 1; o < 16; o <<= 1) {
           a0[c] += __shfl_xor_sync(0xffffffffu, a0[c], o);
           a1[c] += __shfl_xor_sync(0xffffffffu, a1[c], o);
         }
@@ -160,14 +152,14 @@ mlp_head_train_kernel(const HeadParams p) {
       db_acc += sacc;
     }
 
-    const int k4 = t & 127, grp = t >> 7;  // two groups of 128 threads; thread owns columns 4*k4..4*k4+3
+    const int k4 = t & 127, grp = t >> 7;  // four groups of 128 threads; thread owns columns 4*k4..4*k4+3
     if (k4 < K4) {
-      // ---- C: dH = (dz W) masked by H > 0, rows grp*32 .. grp*32+31
+      // ---- C: dH = (dz W) masked by H > 0, rows grp*16 .. grp*16+15
       {
         float4 wr[C];
 #pragma unroll
         for (int c = 0; c < C; ++c) wr[c] = *reinterpret_cast<const float4*>(sw + c * LD + 4 * k4);
-        for (int r = grp * 32; r < grp * 32 + 32; ++r) {
+        for (int r = grp * 16; r < grp * 16 + 16; ++r) {
           const int row = row0 + r;
           if (row >= p.rows) break;
           float d[HD_DZ_LD];
@@ -228,33 +220,52 @@ mlp_head_train_kernel(const HeadParams p) {
   }
 }
 
-// Sums the per-block partials in block order (reproducible): one thread per dW element, plus db and loss.
+// Sums the per-block partials (reproducibly: the order depends only on the grid). A block owns 32 dW
+// elements; its 8 warps each add a strided eighth of the partials with all loads in flight, then the
+// eight subtotals are added in warp order. The last block also reduces db and the loss.
 __global__ void __launch_bounds__(256)
 mlp_head_reduce_kernel(const float* __restrict__ dw_partial, const float* __restrict__ db_partial,
                        const float* __restrict__ loss_partial, int nblocks, int CK, int C, int rows, float* __restrict__ dw,
                        float* __restrict__ db, float* __restrict__ loss) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < CK) {
+  __shared__ float s_part[8][32];
+  {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i = blockIdx.x * 32 + lane;
     float acc = 0.f;
-    for (int b0 = 0; b0 < nblocks; b0 += 8) {
-      float v[8];
+    if (i < CK) {
+      for (int b0 = warp; b0 < nblocks; b0 += 8 * 8) {
+        float v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = (b0 + u < nblocks) ? __ldcg(dw_partial + static_cast<size_t>(b0 + u) * CK + i) : 0.f;
+        for (int u = 0; u < 8; ++u) {
+          const int b = b0 + 8 * u;
+          v[u] = b < nblocks ? __ldcg(dw_partial + static_cast<size_t>(b) * CK + i) : 0.f;
+        }
 #pragma unroll
-      for (int u = 0; u < 8; ++u) acc += v[u];
+        for (int u = 0; u < 8; ++u) acc += v[u];
+      }
     }
-    dw[i] = acc;
+    s_part[warp][lane] = acc;
+    __syncthreads();
+    if (warp == 0 && i < CK) {
+      float tot = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) tot += s_part[w][lane];
+      dw[i] = tot;
+    }
   }
-  if (blockIdx.x == 0 && threadIdx.x < 32) {
-    if (threadIdx.x < C) {
+  if (blockIdx.x == gridDim.x - 1) {
+    // db and the loss: a warp per class, lanes stride over the block partials (loads in flight together),
+    // then a fixed xor tree -> reproducible
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int c = warp; c <= C; c += 8) {             // c == C is the loss
       float acc = 0.f;
-      for (int b = 0; b < nblocks; ++b) acc += __ldcg(db_partial + b * 16 + threadIdx.x);
-      db[threadIdx.x] = acc;
-    }
-    if (threadIdx.x == 31) {
-      float acc = 0.f;
-      for (int b = 0; b < nblocks; ++b) acc += __ldcg(loss_partial + b);
-      *loss = acc / static_cast<float>(rows);
+      for (int b = lane; b < nblocks; b += 32) acc += (c < C) ? __ldcg(db_partial + b * 16 + c) : __ldcg(loss_partial + b);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (lane == 0) {
+        if (c < C) db[c] = acc;
+        else *loss = acc / static_cast<float>(rows);
+      }
     }
   }
 }
@@ -307,7 +318,7 @@ RTDC_API int rtdc_mlp_head_train(const float* h, int ldh, const float* w, const 
   }
   RTDC_CUDA_CHECK(cudaGetLastError());
   const int CK = classes * K;
-  mlp_head_reduce_kernel<<<(CK + 255) / 256, 256, 0, st>>>(p.dw_partial, p.db_partial, p.loss_partial, grid, CK, classes, rows, dw, db, loss);
+  mlp_head_reduce_kernel<<<(CK + 31) / 32, 256, 0, st>>>(p.dw_partial, p.db_partial, p.loss_partial, grid, CK, classes, rows, dw, db, loss);
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;
 }
