@@ -92,7 +92,8 @@ int rtdc_softmax_ce(const float* logits, int ldz, const int64_t* labels, int row
 size_t rtdc_mlp_head_scratch_bytes(int rows, int K, int classes);
 int rtdc_mlp_head_train(const float* h, int ldh, const float* w, const float* bias, const int64_t* labels, int rows,
                         int K, int classes, float grad_scale, float mask_scale, float* dh, int lddh, float* dw,
-                        float* db, float* loss, void* scratch, size_t scratch_bytes, void* stream);
+                        float* db, float* loss, float* db_below /* [K] column sums of dh, or NULL */,
+                        void* scratch, size_t scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Column sums of a [rows, cols] fp32 matrix (bias gradients, K6): out[c] = sum_r x[r*ld + c].

@@ -187,7 +187,7 @@ softmax_ce_kernel(const float* __restrict__ logits, int ldz, const long long* __
 // last block per column group sums the slabs in order.
 constexpr int CS_THREADS = 256;
 constexpr int CS_COLS = 128;     // columns per block: 32 lanes x float4
-constexpr int CS_MAX_SLABS = 64;
+constexpr int CS_MAX_SLABS = 64;   // (the built-in scratch of rtdc_colsum_noalloc is sized for this)
 
 __global__ void __launch_bounds__(CS_THREADS)
 colsum_kernel(const float* __restrict__ x, int ld, int rows, int cols, float* __restrict__ out, float* partial,

@@ -33,6 +33,7 @@ struct HeadParams {
   float* dw_partial;              // [grid][C][K]
   float* db_partial;              // [grid][16]
   float* loss_partial;            // [grid]
+  float* dbh_partial;             // [grid][K]: column sums of dh (bias gradient of the layer below), or null
 };
 
 template <int C>
@@ -60,6 +61,7 @@ mlp_head_train_kernel(const HeadParams p) {
 #pragma unroll
   for (int c = 0; c < CH; ++c) dw_acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
   float db_acc = 0.f;                      // thread t < C owns class t
+  float4 dbh_acc = make_float4(0.f, 0.f, 0.f, 0.f);   // column sums of dh over this thread's rows
   float loss_acc = 0.f;
 
   const int tiles = (p.rows + HD_ROWS - 1) / HD_ROWS;
@@ -180,6 +182,7 @@ mlp_head_train_kernel(const HeadParams p) {
           o.z = hv.z > 0.f ? o.z * p.mask_scale : 0.f;
           o.w = hv.w > 0.f ? o.w * p.mask_scale : 0.f;
           *reinterpret_cast<float4*>(p.dh + static_cast<size_t>(row) * p.lddh + 4 * k4) = o;
+          dbh_acc.x += o.x; dbh_acc.y += o.y; dbh_acc.z += o.z; dbh_acc.w += o.w;
         }
       }
       // ---- D: dW[c][k] += sum_r dz[r][c] * H[r][k], classes grp*CH .. grp*CH+CH-1
@@ -207,6 +210,20 @@ mlp_head_train_kernel(const HeadParams p) {
           *reinterpret_cast<float4*>(p.dw_partial + (static_cast<size_t>(blockIdx.x) * C + cc) * K + 4 * k4) = dw_acc[c];
       }
     }
+    if (p.dbh_partial != nullptr) {
+      __syncthreads();                     // everyone is done with the H tile: reuse it as a [4][K] staging area
+      if (k4 < K4) *reinterpret_cast<float4*>(sh + grp * LD + 4 * k4) = dbh_acc;
+      __syncthreads();
+      if (grp == 0 && k4 < K4) {
+        float4 tot = *reinterpret_cast<const float4*>(sh + 4 * k4);
+#pragma unroll
+        for (int g2 = 1; g2 < 4; ++g2) {
+          const float4 u = *reinterpret_cast<const float4*>(sh + g2 * LD + 4 * k4);
+          tot.x += u.x; tot.y += u.y; tot.z += u.z; tot.w += u.w;
+        }
+        *reinterpret_cast<float4*>(p.dbh_partial + static_cast<size_t>(blockIdx.x) * K + 4 * k4) = tot;
+      }
+    }
     if (t < 16) p.db_partial[blockIdx.x * 16 + t] = t < C ? db_acc : 0.f;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) loss_acc += __shfl_xor_sync(0xffffffffu, loss_acc, o);
@@ -226,19 +243,28 @@ mlp_head_train_kernel(const HeadParams p) {
 __global__ void __launch_bounds__(256)
 mlp_head_reduce_kernel(const float* __restrict__ dw_partial, const float* __restrict__ db_partial,
                        const float* __restrict__ loss_partial, int nblocks, int CK, int C, int rows, float* __restrict__ dw,
-                       float* __restrict__ db, float* __restrict__ loss) {
+                       float* __restrict__ db, float* __restrict__ loss, const float* __restrict__ dbh_partial, int K,
+                       float* __restrict__ dbh) {
   __shared__ float s_part[8][32];
   {
+    // elements [0, CK) are dW, elements [CK, CK + K) are the bias gradient of the layer below (when requested)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int i = blockIdx.x * 32 + lane;
+    int i = blockIdx.x * 32 + lane;
+    const int total = CK + (dbh_partial != nullptr ? K : 0);
+    const bool second = i >= CK;
+    const float* src = second ? dbh_partial : dw_partial;
+    float* dst = second ? dbh : dw;
+    const int stride = second ? K : CK;
+    const bool live = i < total;
+    if (second) i -= CK;
     float acc = 0.f;
-    if (i < CK) {
+    if (live) {
       for (int b0 = warp; b0 < nblocks; b0 += 8 * 8) {
         float v[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
           const int b = b0 + 8 * u;
-          v[u] = b < nblocks ? __ldcg(dw_partial + static_cast<size_t>(b) * CK + i) : 0.f;
+          v[u] = b < nblocks ? __ldcg(src + static_cast<size_t>(b) * stride + i) : 0.f;
         }
 #pragma unroll
         for (int u = 0; u < 8; ++u) acc += v[u];
@@ -246,11 +272,11 @@ mlp_head_reduce_kernel(const float* __restrict__ dw_partial, const float* __rest
     }
     s_part[warp][lane] = acc;
     __syncthreads();
-    if (warp == 0 && i < CK) {
+    if (warp == 0 && live) {
       float tot = 0.f;
 #pragma unroll
       for (int w = 0; w < 8; ++w) tot += s_part[w][lane];
-      dw[i] = tot;
+      dst[i] = tot;
     }
   }
   if (blockIdx.x == gridDim.x - 1) {
@@ -285,12 +311,12 @@ static int head_grid(int rows) {
 
 RTDC_API size_t rtdc_mlp_head_scratch_bytes(int rows, int K, int classes) {
   const size_t g = static_cast<size_t>(head_grid(rows));
-  return g * (static_cast<size_t>(classes) * K + 16 + 4) * sizeof(float) + 256;
+  return g * (static_cast<size_t>(classes) * K + K + 16 + 4) * sizeof(float) + 256;
 }
 
 RTDC_API int rtdc_mlp_head_train(const float* h, int ldh, const float* w, const float* bias, const int64_t* labels, int rows,
                                  int K, int classes, float grad_scale, float mask_scale, float* dh, int lddh, float* dw,
-                                 float* db, float* loss, void* scratch, size_t scratch_bytes, void* stream) {
+                                 float* db, float* loss, float* db_below, void* scratch, size_t scratch_bytes, void* stream) {
   if (!h || !w || !labels || !dh || !dw || !db || !loss) return fail(RTDC_ERR_ARG, "mlp_head_train: null pointer");
   if (rows <= 0 || K <= 0 || K > HD_MAXK || (K & 3) || (ldh & 3) || (lddh & 3))
     return fail(RTDC_ERR_LIMIT, "mlp_head_train: hidden width must be a multiple of 4 and <= %d, row pitches multiples of 4 (K=%d)", HD_MAXK, K);
@@ -307,6 +333,7 @@ RTDC_API int rtdc_mlp_head_train(const float* h, int ldh, const float* w, const 
   p.dw_partial = base;
   p.db_partial = base + static_cast<size_t>(grid) * classes * K;
   p.loss_partial = p.db_partial + static_cast<size_t>(grid) * 16;
+  p.dbh_partial = db_below ? p.loss_partial + ((grid + 3) & ~3) : nullptr;
   const size_t smem = head_smem_bytes(classes, K);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (classes == 10) {
@@ -318,7 +345,9 @@ RTDC_API int rtdc_mlp_head_train(const float* h, int ldh, const float* w, const 
   }
   RTDC_CUDA_CHECK(cudaGetLastError());
   const int CK = classes * K;
-  mlp_head_reduce_kernel<<<(CK + 31) / 32, 256, 0, st>>>(p.dw_partial, p.db_partial, p.loss_partial, grid, CK, classes, rows, dw, db, loss);
+  const int total = CK + (db_below ? K : 0);
+  mlp_head_reduce_kernel<<<(total + 31) / 32, 256, 0, st>>>(p.dw_partial, p.db_partial, p.loss_partial, grid, CK, classes, rows, dw, db, loss,
+                                                          p.dbh_partial, K, db_below);
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;
 }

@@ -65,7 +65,7 @@ def _declare(lib):
     lib.rtdc_softmax_ce.argtypes = [vp, i, vp, i, i, vp, vp, f, i, vp, vp, vp, vp, sz, vp]
     lib.rtdc_mlp_head_scratch_bytes.argtypes = [i, i, i]
     lib.rtdc_mlp_head_scratch_bytes.restype = sz
-    lib.rtdc_mlp_head_train.argtypes = [vp, i, vp, vp, vp, i, i, i, f, f, vp, i, vp, vp, vp, vp, sz, vp]
+    lib.rtdc_mlp_head_train.argtypes = [vp, i, vp, vp, vp, i, i, i, f, f, vp, i, vp, vp, vp, vp, vp, sz, vp]
     lib.rtdc_mlp_head_train.restype = i
     lib.rtdc_colsum_scratch_bytes.argtypes = [i, i]
     lib.rtdc_colsum_scratch_bytes.restype = sz

@@ -52,10 +52,12 @@ def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor, *, classes
 
 def mlp_head_train(h: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], labels: torch.Tensor, *,
                    dh: torch.Tensor, dw: torch.Tensor, db: torch.Tensor, loss: Optional[torch.Tensor] = None,
-                   grad_scale: Optional[float] = None, mask_scale: float = 1.0, stream=None) -> torch.Tensor:
+                   grad_scale: Optional[float] = None, mask_scale: float = 1.0, db_below: Optional[torch.Tensor] = None,
+                   stream=None) -> torch.Tensor:
     """Fused last layer for training: ``z = relu(h @ weight.T + bias)``, mean cross-entropy, and the layer's
     backward (``dw``, ``db``, ``dh = (dz @ weight) * (h > 0) * mask_scale``) in one pass over ``h``.
-    ``weight`` is ``[classes, K]`` with 10 or 16 classes and ``K <= 512``."""
+    ``weight`` is ``[classes, K]`` with 10 or 16 classes and ``K <= 512``. ``db_below[K]`` optionally receives the
+    column sums of ``dh`` (the bias gradient of the layer that produced ``h``)."""
     rows, K = h.shape
     classes = weight.shape[0]
     if loss is None:
@@ -65,7 +67,8 @@ def mlp_head_train(h: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.T
     gs = (1.0 / rows) if grad_scale is None else grad_scale
     _lib.check(lib.rtdc_mlp_head_train(h.data_ptr(), h.stride(0), weight.data_ptr(), bias.data_ptr() if bias is not None else None,
                                        labels.data_ptr(), rows, K, classes, gs, mask_scale, dh.data_ptr(), dh.stride(0),
-                                       dw.data_ptr(), db.data_ptr(), loss.data_ptr(), ws.data_ptr(), ws.numel(),
+                                       dw.data_ptr(), db.data_ptr(), loss.data_ptr(),
+                                       db_below.data_ptr() if db_below is not None else None, ws.data_ptr(), ws.numel(),
                                        _lib.stream_ptr(stream)))
     return loss
 

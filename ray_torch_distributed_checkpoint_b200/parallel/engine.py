@@ -161,7 +161,7 @@ class MLPTrainEngine:
         if fused_head:
             # layer 3 forward + loss + layer 3 backward in one pass over h2 (exact fp32 on the CUDA cores)
             ops.mlp_head_train(self.h2, self.W[2], self.b[2], self.y, dh=self.dh2, dw=self.dW[2], db=self.db[2], loss=self.loss,
-                               grad_scale=1.0 / B, mask_scale=inv_keep, stream=s); n += 2
+                               grad_scale=1.0 / B, mask_scale=inv_keep, db_below=self.db[1], stream=s); n += 2   # also emits db2
         else:
             ops.softmax_cross_entropy(self.z, self.y, classes=self.d_out, dlogits=self.dz, grad_scale=1.0 / B, relu_mask=True,
                                       loss_out=self.loss, dbias_out=self.db[2], stream=s); n += 1   # also emits db3
@@ -170,7 +170,8 @@ class MLPTrainEngine:
                              precision=prec, stream=s); n += 1
         # layer 2
         ops.linear_wgrad(self.dh2, self.h1, out=self.dW[1], precision=prec, stream=s); n += 2
-        ops.colsum(self.dh2, out=self.db[1], stream=s); n += 1
+        if not fused_head:
+            ops.colsum(self.dh2, out=self.db[1], stream=s); n += 1
         launched = set()
         if self.bucket_of_layer[1] != self.bucket_of_layer[0]:
             self._reduce_bucket(self.bucket_of_layer[1], s); launched.add(self.bucket_of_layer[1]); n += self.world > 1

@@ -119,7 +119,8 @@ def test_fused_mlp_head_matches_autograd(rows, classes):
     y = torch.randint(0, classes, (rows,), device="cuda", generator=g)
     dh = torch.full((rows, K), 3.0, device="cuda"); dw = torch.empty(classes, K, device="cuda"); db = torch.empty(classes, device="cuda")
     for _ in range(2):
-        loss = ops.mlp_head_train(h, w, b, y, dh=dh, dw=dw, db=db, mask_scale=1 / (1 - p))
+        dbh = torch.empty(K, device="cuda")
+        loss = ops.mlp_head_train(h, w, b, y, dh=dh, dw=dw, db=db, mask_scale=1 / (1 - p), db_below=dbh)
     hr = h.double().requires_grad_(True); wr = w.double().requires_grad_(True); br = b.double().requires_grad_(True)
     ref = F.cross_entropy(torch.relu(hr @ wr.T + br), y)
     ref.backward()
@@ -128,3 +129,4 @@ def test_fused_mlp_head_matches_autograd(rows, classes):
     assert torch.allclose(dh.double(), ref_dh, rtol=1e-4, atol=1e-9)
     assert (dw.double() - wr.grad).norm() / wr.grad.norm() < 1e-5
     assert (db.double() - br.grad).norm() / br.grad.norm() < 1e-5
+    assert (dbh.double() - ref_dh.sum(0)).norm() / ref_dh.sum(0).norm() < 1e-5
