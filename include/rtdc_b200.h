@@ -55,6 +55,10 @@ typedef struct rtdc_gemm_desc {
   int bn;                 /* N tile (0 = choose) */
   int splits;             /* split-K factor (0 = choose). >1 needs scratch */
   float* scratch; size_t scratch_bytes; /* split-K partial tiles, see rtdc_gemm_scratch_bytes */
+  /* optional fused column sums of the output (bias gradient of the layer that consumes it): the epilogue writes, for
+   * every 32-row group g of the output, sum_rows out[rows of g, n] to colsum_partial[g*ld_colsum + n]
+   * (4*ceil(M/128) groups; rows past M contribute nothing). Sum those rows (e.g. rtdc_colsum) to get the total. */
+  float* colsum_partial; int ld_colsum;
 } rtdc_gemm_desc;
 
 /* Bytes of scratch rtdc_gemm needs for this descriptor (0 when it will not split K): room for the

@@ -50,6 +50,7 @@ struct GemmParams {
   const float* mask_src; int ldm; float mask_scale;
   float* scratch;
   int debug;  // timing experiments only (RTDC_GEMM_DEBUG): 1 = no TMA loads, 2 = no MMAs, 4 = no global stores, 8 = no split pass, 16 = no proxy fence
+  float* colsum_partial; int ld_colsum;   // optional: per (m_tile, warp) column sums of the output tile rows, [4*m_tiles][ld]
   int tma_store;         // epilogue goes through smem + cp.async.bulk.tensor stores (tmOut valid)
   long long* dbg_times;  // RTDC_GEMM_DEBUG_BUF: per-CTA clock64 stamps [grid][8]
 };
@@ -184,6 +185,16 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
         tma_store_commit();
       }
       ++stores_issued;
+      if (p.colsum_partial != nullptr) {
+        // column sums of this warp's 32 x 32 box straight from the staged tile (lane = column; the swizzle
+        // makes the 32 lanes hit 32 different banks): the bias gradient costs no extra pass over HBM
+        const int valid = min(32, p.M - (m0 + wq * 32));
+        float cs = 0.f;
+        for (int rr = 0; rr < valid; ++rr)
+          cs += *reinterpret_cast<const float*>(box + rr * 128 + ((((lane >> 2) ^ (rr & 7))) << 4) + ((lane & 3) << 2));
+        if (col0 + lane < p.N)
+          p.colsum_partial[static_cast<size_t>((m0 / BM) * 4 + wq) * p.ld_colsum + col0 + lane] = cs;
+      }
     } else if (row < p.M) {
       float* dst = p.out + static_cast<size_t>(row) * p.ldo + col0;
       const int rem = n_cols_out - c * 32;
@@ -817,7 +828,7 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
       if (splits < 1) splits = 1;
     }
   }
-  if (splits > 1 && (d->drop_p > 0.f || d->mask_src != nullptr)) splits = 1;  // those epilogues need the full sum in TMEM
+  if (splits > 1 && (d->drop_p > 0.f || d->mask_src != nullptr || d->colsum_partial != nullptr)) splits = 1;  // those epilogues need the full sum in TMEM
   if (splits > pl->num_kb) splits = pl->num_kb;
   pl->kb_per_split = ceil_div(pl->num_kb, splits);
   pl->splits = ceil_div(pl->num_kb, pl->kb_per_split);  // no empty split
@@ -927,6 +938,11 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
     rc = make_map(&to, d->out, n_store, d->M, d->ldo, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != RTDC_OK) return rc;
     gp.tma_store = 1;
+  }
+  if (d->colsum_partial != nullptr) {
+    if (!gp.tma_store || pl.splits > 1) return fail(RTDC_ERR_ARG, "colsum_partial needs an aligned output (TMA-store epilogue) and no K split");
+    if (d->ld_colsum < d->N) return fail(RTDC_ERR_ARG, "ld_colsum (%d) smaller than N (%d)", d->ld_colsum, d->N);
+    gp.colsum_partial = d->colsum_partial; gp.ld_colsum = d->ld_colsum;
   }
   if (const char* dbg = getenv("RTDC_GEMM_DEBUG")) gp.debug = atoi(dbg);
   if (const char* dbg = getenv("RTDC_GEMM_DEBUG_BUF")) gp.dbg_times = reinterpret_cast<long long*>(strtoull(dbg, nullptr, 0));

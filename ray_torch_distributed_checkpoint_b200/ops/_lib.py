@@ -36,6 +36,7 @@ class GemmDesc(C.Structure):
         ("bn", C.c_int),
         ("splits", C.c_int),
         ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
+        ("colsum_partial", C.c_void_p), ("ld_colsum", C.c_int),
     ]
 
 

@@ -48,7 +48,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
          drop_p: float = 0.0, seed: int = 0, step: int = 0, step_tensor: Optional[torch.Tensor] = None, salt: int = 0,
          mask_src: Optional[torch.Tensor] = None, mask_scale: float = 1.0,
          n_store: Optional[int] = None, precision: int = PRECISION_FP32, bn: int = 0, splits: int = 0,
-         stream=None) -> torch.Tensor:
+         colsum_partial: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
     """``out[M,N] = epilogue(sum_k A(m,k) B(n,k))`` on the tensor cores.
 
     ``a`` is ``[M,K]`` (``a_mn=False``) or ``[K,M]`` (``a_mn=True``); ``b`` is ``[N,K]`` or ``[K,N]``.
@@ -79,6 +79,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
         d.mask_src, d.ldm, d.mask_scale = mask_src.data_ptr(), mask_src.stride(0), float(mask_scale)
     d.precision = precision
     d.bn, d.splits = bn, splits
+    if colsum_partial is not None:
+        if colsum_partial.shape[0] < 4 * ((M + 127) // 128) or colsum_partial.dtype != torch.float32:
+            raise ValueError("colsum_partial must be float32 with at least 4*ceil(M/128) rows")
+        d.colsum_partial, d.ld_colsum = colsum_partial.data_ptr(), colsum_partial.stride(0)
     lib = _lib.load()
     need = lib.rtdc_gemm_scratch_bytes(C.byref(d))
     if need:
@@ -109,7 +113,8 @@ def linear_forward(x, weight, bias=None, *, relu=False, drop_p=0.0, seed=0, step
                 step_tensor=step_tensor, salt=salt, n_store=n_store, precision=precision, stream=stream)
 
 
-def linear_dgrad(dy, weight, *, N_out=None, mask_src=None, mask_scale=1.0, out=None, precision=PRECISION_FP32, stream=None):
+def linear_dgrad(dy, weight, *, N_out=None, mask_src=None, mask_scale=1.0, out=None, precision=PRECISION_FP32,
+                 colsum_partial=None, stream=None):
     """``dx = (dy @ weight) * (mask_src > 0) * mask_scale`` (K6 dgrad + ReLU/dropout backward of the
     layer below). ``dy`` may be stored wider than ``N_out`` columns (zero padded)."""
     n_out = weight.shape[0] if N_out is None else N_out
@@ -117,7 +122,7 @@ def linear_dgrad(dy, weight, *, N_out=None, mask_src=None, mask_scale=1.0, out=N
     if out is None:
         out = torch.empty(B, K_in, dtype=torch.float32, device=dy.device)
     return gemm(dy, weight, out, b_mn=True, M=B, N=K_in, K=n_out, mask_src=mask_src, mask_scale=mask_scale,
-                precision=precision, stream=stream)
+                precision=precision, colsum_partial=colsum_partial, stream=stream)
 
 
 def linear_wgrad(dy, x, *, N_out=None, out=None, precision=PRECISION_FP32, splits=0, stream=None):

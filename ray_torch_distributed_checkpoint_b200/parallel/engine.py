@@ -100,6 +100,7 @@ class MLPTrainEngine:
         self.dz = torch.zeros(B, _LOGIT_LD, device=dev)
         self.dh2 = torch.empty(B, self.d_h, device=dev)
         self.dh1 = torch.empty(B, self.d_h, device=dev)
+        self.dh1_colsum = torch.zeros(4 * ((B + 127) // 128), self.d_h, device=dev)
         self.loss = torch.zeros((), device=dev)
         self.step_counter = torch.zeros(1, dtype=torch.int32, device=dev)
         self.eval_loss_sum = torch.zeros((), device=dev)
@@ -175,10 +176,12 @@ class MLPTrainEngine:
         launched = set()
         if self.bucket_of_layer[1] != self.bucket_of_layer[0]:
             self._reduce_bucket(self.bucket_of_layer[1], s); launched.add(self.bucket_of_layer[1]); n += self.world > 1
-        ops.linear_dgrad(self.dh2, self.W[1], mask_src=self.h1, mask_scale=inv_keep, out=self.dh1, precision=prec, stream=s); n += 1
+        # dgrad2 also leaves per-32-row column sums of dh1 (592 x 512 instead of 18944 x 512 to sum for db1)
+        ops.linear_dgrad(self.dh2, self.W[1], mask_src=self.h1, mask_scale=inv_keep, out=self.dh1, precision=prec,
+                         colsum_partial=self.dh1_colsum, stream=s); n += 1
         # layer 1 (its input needs no gradient)
         ops.linear_wgrad(self.dh1, self.x, out=self.dW[0], precision=prec, stream=s); n += 2
-        ops.colsum(self.dh1, out=self.db[0], stream=s); n += 1
+        ops.colsum(self.dh1_colsum, out=self.db[0], stream=s); n += 1
         for b in range(len(self.buckets)):
             if b not in launched:
                 self._reduce_bucket(b, s); n += self.world > 1

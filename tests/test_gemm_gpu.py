@@ -125,3 +125,17 @@ def test_plan_and_errors():
     w = torch.randn(32, 30, device="cuda")
     with pytest.raises(ops.RtdcError):
         ops.linear_forward(x, w)
+
+
+def test_dgrad_fused_column_sums():
+    ops = _ops()
+    B, n_out, k_in = 1000, 512, 512
+    g = torch.Generator(device="cuda").manual_seed(8)
+    dy = torch.randn(B, n_out, device="cuda", generator=g)
+    w = torch.randn(n_out, k_in, device="cuda", generator=g) * 0.05
+    h = torch.relu(torch.randn(B, k_in, device="cuda", generator=g))
+    part = torch.full((4 * ((B + 127) // 128), k_in), 7.0, device="cuda")
+    dx = ops.linear_dgrad(dy, w, mask_src=h, mask_scale=4 / 3, colsum_partial=part)
+    groups = (B + 31) // 32
+    assert torch.allclose(part[:groups].sum(0).double(), dx.double().sum(0), rtol=1e-4, atol=1e-3)
+    assert torch.allclose(ops.colsum(part[:groups].contiguous()).double(), dx.double().sum(0), rtol=1e-4, atol=1e-3)
