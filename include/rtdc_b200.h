@@ -59,7 +59,22 @@ typedef struct rtdc_gemm_desc {
    * every 32-row group g of the output, sum_rows out[rows of g, n] to colsum_partial[g*ld_colsum + n]
    * (4*ceil(M/128) groups; rows past M contribute nothing). Sum those rows (e.g. rtdc_colsum) to get the total. */
   float* colsum_partial; int ld_colsum;
+  /* optional exact-operand / affine-input folding (3xTF32 only). a_exact / b_exact != 0 promise that every element of
+   * that operand has its low 13 mantissa bits clear (e.g. small integers such as raw uint8 pixels widened to fp32), so
+   * the operand needs no low-order correction pass: the kernel skips its split and one of the three MMAs per K step
+   * with no loss of accuracy. A broken promise silently degrades that operand to tf32 precision.
+   * The accumulator is then mapped as  acc*alpha (alpha == 0 means 1)  + bias[n] + row_bias[m]*row_bias_scale
+   * before relu/dropout/mask, which lets a caller fold an input normalisation x = s*raw + t into the layer:
+   *   forward  W x + b          = s*(W raw) + (b + t*rowsum(W))          -> alpha = s, bias = rtdc_fold_input_bias(...)
+   *   wgrad    dY^T x           = s*(dY^T raw) + t*colsum(dY) 1^T        -> alpha = s, row_bias = db, row_bias_scale = t */
+  int a_exact, b_exact;
+  float alpha;
+  const float* row_bias; float row_bias_scale;
 } rtdc_gemm_desc;
+
+/* out[n] = bias[n] (0 when NULL) + t * sum_k w[n*ldw + k], n < rows: the effective bias of a Linear layer whose input
+ * normalisation x = s*raw + t has been folded into the GEMM (see rtdc_gemm_desc.alpha). One warp per row. */
+int rtdc_fold_input_bias(const float* w, int ldw, int rows, int cols, const float* bias, float t, float* out, void* stream);
 
 /* Bytes of scratch rtdc_gemm needs for this descriptor (0 when it will not split K): room for the
  * per-split partial tiles, which a second kernel sums in split order. Contents need no initialisation.
@@ -129,6 +144,9 @@ int rtdc_colsum_noalloc(const float* x, int ld, int rows, int cols, float* out, 
 
 /* uint8 pixels -> normalised fp32 ((x/255 - mean)/std; ref: my_ray_module.py:38 ToTensor+Normalize). */
 int rtdc_u8_normalize(const uint8_t* src, float* dst, size_t n, float mean, float std, void* stream);
+/* uint8 -> fp32 x*scale + shift (one fma). scale = 1, shift = 0 widens raw pixels exactly, the form the exact-operand
+ * GEMM path (rtdc_gemm_desc.a_exact / b_exact) consumes. */
+int rtdc_u8_affine(const uint8_t* src, float* dst, size_t n, float scale, float shift, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Fused optimizer steps over a flat parameter arena (K7). hyper points to device memory so a

@@ -527,6 +527,55 @@ RTDC_API int rtdc_u8_normalize(const uint8_t* src, float* dst, size_t n, float m
   return RTDC_OK;
 }
 
+RTDC_API int rtdc_u8_affine(const uint8_t* src, float* dst, size_t n, float scale, float shift, void* stream) {
+  if (!src || !dst) return fail(RTDC_ERR_ARG, "u8_affine: null pointer");
+  if (n == 0) return RTDC_OK;
+  if ((reinterpret_cast<uintptr_t>(src) & 15u) || (reinterpret_cast<uintptr_t>(dst) & 15u)) return fail(RTDC_ERR_ARG, "u8_affine: pointers must be 16-byte aligned");
+  u8_normalize_kernel<<<grid_for(n / 16 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(src, dst, n, scale, shift);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
+namespace rtdc {
+// out[n] = bias[n] + t * sum_k w[n, k]: one warp per row, 4 independent float4 loads per lane in flight,
+// fixed summation order (lane-strided partials, then a shuffle tree).
+__global__ void __launch_bounds__(256)
+fold_input_bias_kernel(const float* __restrict__ w, int ldw, int rows, int cols, const float* __restrict__ bias, float t,
+                       float* __restrict__ out) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const float* wr = w + static_cast<size_t>(row) * ldw;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  if ((ldw & 3) == 0 && (reinterpret_cast<uintptr_t>(w) & 15u) == 0) {
+    const int nv = cols >> 2;
+    for (int i0 = lane; i0 < nv; i0 += 128) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        v[u] = (i0 + 32 * u < nv) ? __ldg(reinterpret_cast<const float4*>(wr) + i0 + 32 * u) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) acc[u] += (v[u].x + v[u].y) + (v[u].z + v[u].w);
+    }
+    for (int k = (nv << 2) + lane; k < cols; k += 32) acc[0] += __ldg(wr + k);
+  } else {
+    for (int k = lane; k < cols; k += 32) acc[0] += __ldg(wr + k);
+  }
+  float sum = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) out[row] = fmaf(t, sum, bias != nullptr ? __ldg(bias + row) : 0.f);
+}
+}  // namespace rtdc
+
+RTDC_API int rtdc_fold_input_bias(const float* w, int ldw, int rows, int cols, const float* bias, float t, float* out, void* stream) {
+  if (!w || !out) return fail(RTDC_ERR_ARG, "fold_input_bias: null pointer");
+  if (rows <= 0 || cols <= 0 || ldw < cols) return fail(RTDC_ERR_ARG, "fold_input_bias: bad shape (%d x %d, ld %d)", rows, cols, ldw);
+  rtdc::fold_input_bias_kernel<<<(rows + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(w, ldw, rows, cols, bias, t, out);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
 RTDC_API int rtdc_sgd_step(float* p, const float* g, float* m, size_t n, const rtdc_sgd_hyper* hyper_dev, void* stream) {
   if (!p || !g || !hyper_dev) return fail(RTDC_ERR_ARG, "sgd_step: null pointer");
   if (n == 0) return RTDC_OK;

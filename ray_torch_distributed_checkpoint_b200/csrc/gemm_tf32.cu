@@ -51,6 +51,11 @@ struct GemmParams {
   float* scratch;
   int debug;  // timing experiments only (RTDC_GEMM_DEBUG): 1 = no TMA loads, 2 = no MMAs, 4 = no global stores, 8 = no split pass, 16 = no proxy fence
   float* colsum_partial; int ld_colsum;   // optional: per (m_tile, warp) column sums of the output tile rows, [4*m_tiles][ld]
+  // exact operands (no tail tile, one MMA fewer per K step) and the affine map of the accumulator
+  int a_exact, b_exact;
+  uint32_t a_tail_off, b_tail_off;        // tail tiles, bytes from the start of a stage
+  uint32_t split_lo_vec, split_hi_vec;    // float4 range of the raw tiles the splitters have to process
+  float alpha; const float* row_bias; float row_bias_scale;
   int tma_store;         // epilogue goes through smem + cp.async.bulk.tensor stores (tmOut valid)
   long long* dbg_times;  // RTDC_GEMM_DEBUG_BUF: per-CTA clock64 stamps [grid][8]
 };
@@ -76,6 +81,8 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
   const int n_cols_out = min(p.bn, p.n_store - n0);  // columns to write (valid + zero padding)
   const int n_chunks = (n_cols_out + 31) / 32;
   const int acc_chunks = (umma_n + 31) / 32;         // chunks that hold MMA output
+  const float alpha = p.alpha;
+  const float rb = (p.row_bias != nullptr && row < p.M) ? __ldg(p.row_bias + row) * p.row_bias_scale : 0.f;
   uint32_t r[32];
   if (p.splits > 1) {
     // split-K: park this split's partial tile in scratch; splitk_reduce_kernel sums the splits in
@@ -115,7 +122,7 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
     const int live = umma_n - c * 32;
 #pragma unroll
     for (int q = 0; q < 32; ++q) {
-      float x = (q < live) ? v[q] + s_bias[c * 32 + q] : 0.f;
+      float x = (q < live) ? fmaf(v[q], alpha, s_bias[c * 32 + q]) + rb : 0.f;
       v[q] = relu ? fmaxf(x, 0.f) : x;
     }
     const int col0 = n0 + c * 32;
@@ -185,7 +192,7 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
         tma_store_commit();
       }
       ++stores_issued;
-      if (p.colsum_partial != nullptr) {
+      if (p.colsum_partial != nullptr && m0 < p.M) {   // (a CTA pair's second half can lie entirely past M)
         // column sums of this warp's 32 x 32 box straight from the staged tile (lane = column; the swizzle
         // makes the 32 lanes hit 32 different banks): the bias gradient costs no extra pass over HBM
         const int valid = min(32, p.M - (m0 + wq * 32));
@@ -306,7 +313,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      const uint32_t tail_off = p.a_bytes + p.b_bytes;  // tails live right after the raw tiles
+      const bool a_exact = p.a_exact != 0, b_exact = p.b_exact != 0;
       // K-major: 8-row groups (SW128 for 128-byte rows, SW64 for 64-byte rows). MN-major: 32-wide MN blocks
       // one TMA box apart, 4-row K groups 512 B apart (SW128 with 32-byte atoms: the only MN-major layout
       // tf32 accepts).
@@ -348,11 +355,19 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, b_sbo, b_lt);
               const uint32_t acc = (it > 0 || k > 0) ? 1u : 0u;
               if (NSPLIT == 3) {
-                const uint64_t da_t = umma_smem_desc(sa + tail_off + k * a_kstep, a_lbo, a_sbo, a_lt);
-                const uint64_t db_t = umma_smem_desc(sb + tail_off + k * b_kstep, b_lbo, b_sbo, b_lt);
-                umma_tf32_ss(tmem_acc, da_t, db, idesc, acc);  // small terms first
-                umma_tf32_ss(tmem_acc, da, db_t, idesc, 1u);
-                umma_tf32_ss(tmem_acc, da, db, idesc, 1u);
+                // small terms first; an exact operand has no tail, so its correction MMA is dropped
+                uint32_t acc2 = acc;
+                if (!a_exact) {
+                  const uint64_t da_t = umma_smem_desc(sa + p.a_tail_off + k * a_kstep, a_lbo, a_sbo, a_lt);
+                  umma_tf32_ss(tmem_acc, da_t, db, idesc, acc2);
+                  acc2 = 1u;
+                }
+                if (!b_exact) {
+                  const uint64_t db_t = umma_smem_desc(sa + p.b_tail_off + k * b_kstep, b_lbo, b_sbo, b_lt);
+                  umma_tf32_ss(tmem_acc, da, db_t, idesc, acc2);
+                  acc2 = 1u;
+                }
+                umma_tf32_ss(tmem_acc, da, db, idesc, acc2);
               } else {
                 umma_tf32_ss(tmem_acc, da, db, idesc, acc);
               }
@@ -372,7 +387,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (NSPLIT == 3) {
       const int st = threadIdx.x - 64;  // 0..127
       const uint32_t raw_bytes = p.a_bytes + p.b_bytes;
-      const int nvec = static_cast<int>(raw_bytes >> 4);
+      // raw float4 range to split ([A|B], minus an exact operand); tail[i] pairs with raw[i] for both layouts
+      const int lo = static_cast<int>(p.split_lo_vec), nvec = static_cast<int>(p.split_hi_vec);
       int s = 0;
       uint32_t ph = 0;
       for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
@@ -382,11 +398,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int it = 0; it < n_iters; ++it) {
           mbar_wait(&full_bar[s], ph);
           const float4* raw = reinterpret_cast<const float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes);
-          float4* tail = reinterpret_cast<float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes + raw_bytes);
+          float4* tail = reinterpret_cast<float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes + raw_bytes) - lo;
           // SPLIT_ILP loads are issued back to back before any store: the compiler cannot prove that the
           // tail tile does not alias the raw tile, so a plain loop serialises LDS -> STS -> LDS.
           constexpr int SPLIT_ILP = 6;
-          for (int base = st; base < ((p.debug & 8) ? 0 : nvec); base += SPLIT_THREADS * SPLIT_ILP) {
+          for (int base = lo + st; base < ((p.debug & 8) ? 0 : nvec); base += SPLIT_THREADS * SPLIT_ILP) {
             float4 v[SPLIT_ILP];
 #pragma unroll
             for (int q = 0; q < SPLIT_ILP; ++q) {
@@ -528,11 +544,14 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       for (int u = pair; u < total_units; u += num_pairs) {
         const int tile2 = u % tiles2, split = u / tiles2;
         const int m0 = (tile2 % p.m_tiles2) * (2 * BM) + static_cast<int>(rank) * BM;
-        const int nb0 = (tile2 / p.m_tiles2) * p.bn + static_cast<int>(rank) * half_bn;
+        const int n0 = (tile2 / p.m_tiles2) * p.bn;
+        const int gran2 = B_MN ? 64 : 32;
+        const int umma_n = min(p.bn, (min(p.bn, p.N - n0) + gran2 - 1) / gran2 * gran2);   // this tile's MMA width
+        const int nb0 = n0 + static_cast<int>(rank) * (umma_n >> 1);                          // this CTA's half of it
         const int kb_begin = split * p.kb_per_split;
         const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
         for (int it = 0; it < n_iters; ++it) {
-          if (p.debug & 64) mbar_wait(&empty_bar[s], ph ^ 1u); else mbar_wait_cluster(&empty_bar[s], ph ^ 1u);
+          mbar_wait(&empty_bar[s], ph ^ 1u);
           uint8_t* sa = ring_ptr + static_cast<size_t>(s) * p.stage_bytes;
           uint8_t* sb = sa + p.a_bytes;
           if (p.debug & 1) { mbar_arrive(&full_bar[s]); if (++s == p.stages) { s = 0; ph ^= 1u; } continue; }
@@ -557,7 +576,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (leader CTA only)
     if (lane == 0 && rank == 0) {
-      const uint32_t tail_off = p.a_bytes + p.b_bytes;
+      const bool a_exact = p.a_exact != 0, b_exact = p.b_exact != 0;
       constexpr uint32_t kmajor_sbo = 8u * BK * 4u;
       constexpr uint32_t mn_box = 128u * BK;
       const uint32_t a_lbo = A_MN ? mn_box : 16u, b_lbo = B_MN ? mn_box : 16u;
@@ -565,20 +584,23 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       const uint32_t a_lt = A_MN ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW64;
       const uint32_t b_lt = B_MN ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW64;
       const uint32_t a_kstep = A_MN ? 1024u : 32u, b_kstep = B_MN ? 1024u : 32u;
-      const uint32_t idesc = umma_idesc(UMMA_TF32, A_MN, B_MN, static_cast<uint32_t>(p.bn), 256);
       int s = 0;
       uint32_t ph = 0;
       int j = 0;
       for (int u = pair; u < total_units; u += num_pairs, ++j) {
-        const int split = u / tiles2;
+        const int tile2 = u % tiles2, split = u / tiles2;
         const int kb_begin = split * p.kb_per_split;
         const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
+        const int n0 = (tile2 / p.m_tiles2) * p.bn;
+        const int gran2 = B_MN ? 64 : 32;
+        const int umma_n = min(p.bn, (min(p.bn, p.N - n0) + gran2 - 1) / gran2 * gran2);
+        const uint32_t idesc = umma_idesc(UMMA_TF32, A_MN, B_MN, static_cast<uint32_t>(umma_n), 256);
         const int buf = j & 1;
-        if (p.debug & 64) mbar_wait(&tmem_empty_bar[buf], ((j >> 1) & 1) ^ 1u); else mbar_wait_cluster(&tmem_empty_bar[buf], ((j >> 1) & 1) ^ 1u);
+        mbar_wait(&tmem_empty_bar[buf], ((j >> 1) & 1) ^ 1u);
         tcgen05_fence_after();
         const uint32_t tmem_acc = tmem_base + static_cast<uint32_t>(buf) * MAX_BN;
         for (int it = 0; it < n_iters; ++it) {
-          if (p.debug & 64) mbar_wait(&ready_bar[s], ph); else mbar_wait_cluster(&ready_bar[s], ph);
+          mbar_wait(&ready_bar[s], ph);
           tcgen05_fence_after();
           const uint32_t sa = ring + static_cast<uint32_t>(s) * p.stage_bytes;
           const uint32_t sb = sa + p.a_bytes;
@@ -587,12 +609,18 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
           for (int k = 0; k < ((p.debug & 2) ? 0 : ksteps); ++k) {
             const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, a_sbo, a_lt);
             const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, b_sbo, b_lt);
-            const uint64_t da_t = umma_smem_desc(sa + tail_off + k * a_kstep, a_lbo, a_sbo, a_lt);
-            const uint64_t db_t = umma_smem_desc(sb + tail_off + k * b_kstep, b_lbo, b_sbo, b_lt);
-            const uint32_t acc = (it > 0 || k > 0) ? 1u : 0u;
-            umma_tf32_ss_2cta(tmem_acc, da_t, db, idesc, acc);
-            umma_tf32_ss_2cta(tmem_acc, da, db_t, idesc, 1u);
-            umma_tf32_ss_2cta(tmem_acc, da, db, idesc, 1u);
+            uint32_t acc = (it > 0 || k > 0) ? 1u : 0u;
+            if (!a_exact) {
+              const uint64_t da_t = umma_smem_desc(sa + p.a_tail_off + k * a_kstep, a_lbo, a_sbo, a_lt);
+              umma_tf32_ss_2cta(tmem_acc, da_t, db, idesc, acc);
+              acc = 1u;
+            }
+            if (!b_exact) {
+              const uint64_t db_t = umma_smem_desc(sa + p.b_tail_off + k * b_kstep, b_lbo, b_sbo, b_lt);
+              umma_tf32_ss_2cta(tmem_acc, da, db_t, idesc, acc);
+              acc = 1u;
+            }
+            umma_tf32_ss_2cta(tmem_acc, da, db, idesc, acc);
           }
           tcgen05_commit_2cta(&empty_bar[s], 0x3);        // both CTAs' slots are free once these MMAs have read them
           if (++s == p.stages) { s = 0; ph ^= 1u; }
@@ -605,7 +633,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
     // ------------------------------------------------------------------ splitters (both CTAs, own tiles)
     const int st = threadIdx.x - 64;
     const uint32_t raw_bytes = p.a_bytes + p.b_bytes;
-    const int nvec = static_cast<int>(raw_bytes >> 4);
+    const int lo = static_cast<int>(p.split_lo_vec), nvec = static_cast<int>(p.split_hi_vec);
     int s = 0;
     uint32_t ph = 0;
     for (int u = pair; u < total_units; u += num_pairs) {
@@ -615,9 +643,9 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       for (int it = 0; it < n_iters; ++it) {
         mbar_wait(&full_bar[s], ph);
         const float4* raw = reinterpret_cast<const float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes);
-        float4* tail = reinterpret_cast<float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes + raw_bytes);
+        float4* tail = reinterpret_cast<float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes + raw_bytes) - lo;
         constexpr int SPLIT_ILP = 4;
-        for (int base = st; base < ((p.debug & 8) ? 0 : nvec); base += SPLIT_THREADS * SPLIT_ILP) {
+        for (int base = lo + st; base < ((p.debug & 8) ? 0 : nvec); base += SPLIT_THREADS * SPLIT_ILP) {
           float4 v[SPLIT_ILP];
 #pragma unroll
           for (int q = 0; q < SPLIT_ILP; ++q) {
@@ -658,6 +686,8 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       const int m_tile128 = (tile2 % p.m_tiles2) * 2 + static_cast<int>(rank);
       const int n_tile = tile2 / p.m_tiles2;
       const int m0 = m_tile128 * BM, n0 = n_tile * p.bn;
+      const int gran2 = B_MN ? 64 : 32;
+      const int umma_n = min(p.bn, (min(p.bn, p.N - n0) + gran2 - 1) / gran2 * gran2);
       const int tile128 = m_tile128 < p.m_tiles ? n_tile * p.m_tiles + m_tile128 : -1;   // -1: rows entirely past M
       const int buf = j & 1;
       const uint32_t taddr = tmem_base + static_cast<uint32_t>(buf) * MAX_BN + (static_cast<uint32_t>(wq * 32) << 16);
@@ -665,9 +695,9 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       for (int c = et; c < MAX_BN; c += EPI_THREADS)
         s_bias[c] = (p.bias != nullptr && c < p.bn && n0 + c < p.N) ? __ldg(p.bias + n0 + c) : 0.f;
       named_bar_sync(1, EPI_THREADS);
-      if (p.debug & 64) mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1); else mbar_wait_cluster(&tmem_full_bar[buf], (j >> 1) & 1);
+      mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);
       tcgen05_fence_after();
-      epilogue_unit(p, &tmOut, taddr, p.bn, tile128, split, m0, n0, r_in_tile, lane, wq, s_bias, stage_buf, stores_issued, step,
+      epilogue_unit(p, &tmOut, taddr, umma_n, tile128, split, m0, n0, r_in_tile, lane, wq, s_bias, stage_buf, stores_issued, step,
                     [&]() { if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[buf], 0); });
     }
     if (p.tma_store && lane == 0) tma_store_wait_all();
@@ -685,7 +715,8 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
 // one float4, so both the scratch reads and the output writes are full 128-byte lines.
 __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const float* __restrict__ scratch, int splits, int m_tiles, int bn, int M, int N, int n_store,
-                     float* __restrict__ out, int ldo, const float* __restrict__ bias, int relu) {
+                     float* __restrict__ out, int ldo, const float* __restrict__ bias, int relu, float alpha,
+                     const float* __restrict__ row_bias, float row_bias_scale) {
   const int chunks = (bn + 31) / 32;
   const int tile = blockIdx.x / chunks, c = blockIdx.x % chunks;
   const int m_tile = tile % m_tiles, n_tile = tile / m_tiles;
@@ -708,11 +739,12 @@ splitk_reduce_kernel(const float* __restrict__ scratch, int splits, int m_tiles,
     }
   }
   float v[4] = {acc.x, acc.y, acc.z, acc.w};
+  const float rb = row_bias != nullptr ? __ldg(row_bias + row) * row_bias_scale : 0.f;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     float x = 0.f;
     if (col + j < N) {
-      x = v[j] + (bias != nullptr ? __ldg(bias + col + j) : 0.f);
+      x = fmaf(v[j], alpha, bias != nullptr ? __ldg(bias + col + j) : 0.f) + rb;
       if (relu) x = fmaxf(x, 0.f);
     }
     v[j] = x;
@@ -766,6 +798,7 @@ static int make_map(CUtensorMap* map, const float* base, int inner, int outer, i
 
 struct Plan {
   int two_cta, m_tiles2;
+  int a_exact, b_exact;
   int bk;
   int bn, stages, splits, kb_per_split, num_kb, m_tiles, n_tiles;
   uint32_t a_bytes, b_bytes, stage_bytes;
@@ -786,15 +819,26 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
   if (!d) return fail(RTDC_ERR_ARG, "null descriptor");
   if (d->M <= 0 || d->N <= 0 || d->K <= 0) return fail(RTDC_ERR_ARG, "M, N, K must be positive (got %d, %d, %d)", d->M, d->N, d->K);
   if (d->precision != 1 && d->precision != 3) return fail(RTDC_ERR_ARG, "precision must be 1 (tf32) or 3 (3xTF32)");
-  // CTA pairs (cta_group::2) for the fp32-accurate path when the tile grid is big enough to pair up
+  // CTA pairs (cta_group::2) for the fp32-accurate path: a pair shares one 256-row tile, each CTA stages half of B, so
+  // shared-memory traffic per SM drops by a third and the main loop becomes tensor-bound. Used when the tile grid pairs up
+  // and the coarser N granularity does not cost more padding than it saves. RTDC_GEMM_2CTA=0/1 forces the choice.
   const char* env2 = getenv("RTDC_GEMM_2CTA");
-  const bool two_cta = d->precision == 3 && d->N >= 256 && d->M > BM && (env2 && env2[0] == '1');   // opt-in until validated
+  const int gran2 = d->b_mn ? 64 : 32, gran1 = d->b_mn ? 32 : 16;
+  bool two_cta = d->precision == 3 && d->M > BM && d->N >= 128;
+  if (two_cta && d->bn != 0 && d->bn % gran2 != 0) two_cta = false;
+  if (two_cta && d->bn == 0 && !(env2 && env2[0] == '1')) {
+    const int nt = ceil_div(d->N, MAX_BN);
+    const int bn1 = round_up(ceil_div(d->N, nt), (nt > 1 && gran1 < 32) ? 32 : gran1), bn2 = round_up(ceil_div(d->N, nt), gran2);
+    if (ceil_div(d->N, bn2) * bn2 * 100 > ceil_div(d->N, bn1) * bn1 * 120) two_cta = false;
+  }
+  if (env2 && env2[0] == '0') two_cta = false;
   pl->two_cta = two_cta ? 1 : 0;
   const int gran = two_cta ? (d->b_mn ? 64 : 32) : (d->b_mn ? 32 : 16);
   int bn = d->bn;
   if (bn == 0) {
     const int nt = ceil_div(d->N, MAX_BN);
-    bn = round_up(ceil_div(d->N, nt), gran);
+    // several N tiles: whole 32-column store boxes per tile, so a tile's last box cannot spill into its neighbour
+    bn = round_up(ceil_div(d->N, nt), (nt > 1 && gran < 32) ? 32 : gran);
   }
   if (bn < gran || bn > MAX_BN || bn % gran != 0)
     return fail(RTDC_ERR_ARG, "bn must be a multiple of %d in [%d, %d] (got %d)", gran, gran, MAX_BN, bn);
@@ -808,7 +852,11 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
   pl->num_kb = ceil_div(d->K, pl->bk);
   pl->a_bytes = BM * pl->bk * 4;
   pl->b_bytes = static_cast<uint32_t>(two_cta ? bn / 2 : bn) * pl->bk * 4;   // a CTA of a pair stages half of B
-  pl->stage_bytes = (pl->a_bytes + pl->b_bytes) * (d->precision == 3 ? 2u : 1u);
+  // an operand declared exact needs no tail tile (3xTF32 kernels; the 1-pass kernel has no tails at all)
+  pl->a_exact = (d->precision == 3 && d->a_exact) ? 1 : 0;
+  pl->b_exact = (d->precision == 3 && d->b_exact) ? 1 : 0;
+  pl->stage_bytes = pl->a_bytes + pl->b_bytes;
+  if (d->precision == 3) pl->stage_bytes += (pl->a_exact ? 0u : pl->a_bytes) + (pl->b_exact ? 0u : pl->b_bytes);
   int stages = static_cast<int>((SMEM_LIMIT - STATIC_SMEM_RESERVE - 1024 - EPI_STAGING_BYTES) / pl->stage_bytes);
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages > pl->num_kb) stages = pl->num_kb < 1 ? 1 : pl->num_kb;
@@ -911,6 +959,13 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   gp.bn = pl.bn; gp.stages = pl.stages; gp.splits = pl.splits; gp.kb_per_split = pl.kb_per_split; gp.num_kb = pl.num_kb;
   gp.m_tiles = pl.m_tiles; gp.n_tiles = pl.n_tiles; gp.m_tiles2 = pl.m_tiles2;
   gp.a_bytes = pl.a_bytes; gp.b_bytes = pl.b_bytes; gp.stage_bytes = pl.stage_bytes;
+  gp.a_exact = pl.a_exact; gp.b_exact = pl.b_exact;
+  gp.a_tail_off = pl.a_bytes + pl.b_bytes;
+  gp.b_tail_off = pl.a_bytes + pl.b_bytes + (pl.a_exact ? 0u : pl.a_bytes);
+  gp.split_lo_vec = pl.a_exact ? pl.a_bytes >> 4 : 0u;
+  gp.split_hi_vec = pl.b_exact ? pl.a_bytes >> 4 : (pl.a_bytes + pl.b_bytes) >> 4;
+  gp.alpha = d->alpha == 0.f ? 1.f : d->alpha;
+  gp.row_bias = d->row_bias; gp.row_bias_scale = d->row_bias_scale;
   gp.out = d->out; gp.ldo = d->ldo; gp.n_store = n_store;
   gp.bias = d->bias; gp.relu = d->relu;
   if (d->drop_p > 0.f) {
@@ -934,7 +989,7 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   CUtensorMap to;
   memset(&to, 0, sizeof(to));
   if ((reinterpret_cast<uintptr_t>(d->out) & 15u) == 0 && (static_cast<size_t>(d->ldo) * 4) % 16 == 0 &&
-      !getenv("RTDC_GEMM_NO_TMA_STORE")) {
+      (pl.bn % 32 == 0 || pl.n_tiles == 1) && !getenv("RTDC_GEMM_NO_TMA_STORE")) {
     rc = make_map(&to, d->out, n_store, d->M, d->ldo, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != RTDC_OK) return rc;
     gp.tma_store = 1;
@@ -953,7 +1008,7 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   if (pl.splits > 1) {
     dim3 grid(pl.m_tiles * pl.n_tiles * ((pl.bn + 31) / 32), BM / 32);
     splitk_reduce_kernel<<<grid, 256, 0, st>>>(gp.scratch, pl.splits, pl.m_tiles, pl.bn, d->M, d->N, n_store, d->out, d->ldo,
-                                              d->bias, d->relu);
+                                              d->bias, d->relu, gp.alpha, d->row_bias, d->row_bias_scale);
     RTDC_CUDA_CHECK(cudaGetLastError());
   }
   return RTDC_OK;

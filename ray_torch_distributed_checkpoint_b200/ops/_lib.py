@@ -37,6 +37,9 @@ class GemmDesc(C.Structure):
         ("splits", C.c_int),
         ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
         ("colsum_partial", C.c_void_p), ("ld_colsum", C.c_int),
+        ("a_exact", C.c_int), ("b_exact", C.c_int),
+        ("alpha", C.c_float),
+        ("row_bias", C.c_void_p), ("row_bias_scale", C.c_float),
     ]
 
 
@@ -72,11 +75,14 @@ def _declare(lib):
     lib.rtdc_colsum_scratch_bytes.restype = sz
     lib.rtdc_colsum.argtypes = [vp, i, i, i, vp, vp, sz, vp]
     lib.rtdc_u8_normalize.argtypes = [vp, vp, sz, f, f, vp]
+    lib.rtdc_u8_affine.argtypes = [vp, vp, sz, f, f, vp]
+    lib.rtdc_fold_input_bias.argtypes = [vp, i, i, i, vp, f, vp, vp]
     lib.rtdc_sgd_step.argtypes = [vp, vp, vp, sz, vp, vp]
     lib.rtdc_adam_step.argtypes = [vp, vp, vp, vp, sz, vp, vp]
     lib.rtdc_adam_advance.argtypes = [vp, vp]
     lib.rtdc_counter_advance.argtypes = [vp, vp, vp]
-    for name in ("rtdc_gemm", "rtdc_gemm_plan", "rtdc_softmax_ce", "rtdc_colsum", "rtdc_u8_normalize",
+    for name in ("rtdc_gemm", "rtdc_gemm_plan", "rtdc_softmax_ce", "rtdc_colsum", "rtdc_u8_normalize", "rtdc_u8_affine",
+                 "rtdc_fold_input_bias",
                  "rtdc_sgd_step", "rtdc_adam_step", "rtdc_adam_advance", "rtdc_counter_advance"):
         getattr(lib, name).restype = i
     # optional groups (declared by their own modules once present)

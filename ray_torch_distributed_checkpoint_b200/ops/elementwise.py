@@ -99,6 +99,33 @@ def u8_normalize(src: torch.Tensor, *, mean: float = 0.5, std: float = 0.5, out:
     return out
 
 
+def u8_affine(src: torch.Tensor, *, scale: float = 1.0, shift: float = 0.0, out: Optional[torch.Tensor] = None,
+              stream=None) -> torch.Tensor:
+    """uint8 -> float32 ``x*scale + shift``; the defaults widen raw pixels exactly (every value is then exact in
+    tf32, which is what ``gemm(..., a_exact/b_exact)`` wants)."""
+    if src.dtype != torch.uint8 or not src.is_cuda or not src.is_contiguous():
+        raise ValueError("src must be a contiguous uint8 CUDA tensor")
+    if out is None:
+        out = torch.empty(src.shape, dtype=torch.float32, device=src.device)
+    _lib.check(_lib.load().rtdc_u8_affine(src.data_ptr(), out.data_ptr(), src.numel(), scale, shift, _lib.stream_ptr(stream)))
+    return out
+
+
+def fold_input_bias(weight: torch.Tensor, bias: Optional[torch.Tensor], t: float, *, out: Optional[torch.Tensor] = None,
+                    stream=None) -> torch.Tensor:
+    """``out[n] = bias[n] + t * weight[n, :].sum()``: the bias a Linear layer sees once the input normalisation
+    ``x = s*raw + t`` is folded into its GEMM (``W x + b = s*(W raw) + out``)."""
+    if weight.dtype != torch.float32 or not weight.is_cuda or weight.dim() != 2 or weight.stride(1) != 1:
+        raise ValueError("weight must be a 2-D float32 CUDA tensor with unit inner stride")
+    rows, cols = weight.shape
+    if out is None:
+        out = torch.empty(rows, dtype=torch.float32, device=weight.device)
+    _lib.check(_lib.load().rtdc_fold_input_bias(weight.data_ptr(), weight.stride(0), rows, cols,
+                                                bias.data_ptr() if bias is not None else None, t, out.data_ptr(),
+                                                _lib.stream_ptr(stream)))
+    return out
+
+
 def _hyper_tensor(struct, device) -> torch.Tensor:
     raw = bytes(struct)
     return torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(device)

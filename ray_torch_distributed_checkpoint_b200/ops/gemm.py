@@ -48,12 +48,16 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
          drop_p: float = 0.0, seed: int = 0, step: int = 0, step_tensor: Optional[torch.Tensor] = None, salt: int = 0,
          mask_src: Optional[torch.Tensor] = None, mask_scale: float = 1.0,
          n_store: Optional[int] = None, precision: int = PRECISION_FP32, bn: int = 0, splits: int = 0,
-         colsum_partial: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
+         colsum_partial: Optional[torch.Tensor] = None, a_exact: bool = False, b_exact: bool = False, alpha: float = 1.0,
+         row_bias: Optional[torch.Tensor] = None, row_bias_scale: float = 1.0, stream=None) -> torch.Tensor:
     """``out[M,N] = epilogue(sum_k A(m,k) B(n,k))`` on the tensor cores.
 
     ``a`` is ``[M,K]`` (``a_mn=False``) or ``[K,M]`` (``a_mn=True``); ``b`` is ``[N,K]`` or ``[K,N]``.
     Logical sizes default to the tensor shapes; pass ``M/N/K`` to use fewer rows/columns than stored
-    (padded buffers).
+    (padded buffers). ``a_exact`` / ``b_exact`` promise that the operand's values are exact in tf32 (e.g. raw
+    uint8 pixels widened to fp32) so its 3xTF32 correction pass is skipped; the accumulator is mapped as
+    ``acc*alpha + bias[n] + row_bias[m]*row_bias_scale`` before the activation epilogue (input-normalisation
+    folding, see ``include/rtdc_b200.h``).
     """
     _check(a, "a"); _check(b, "b"); _check(out, "out")
     am, ak = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
@@ -83,6 +87,11 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
         if colsum_partial.shape[0] < 4 * ((M + 127) // 128) or colsum_partial.dtype != torch.float32:
             raise ValueError("colsum_partial must be float32 with at least 4*ceil(M/128) rows")
         d.colsum_partial, d.ld_colsum = colsum_partial.data_ptr(), colsum_partial.stride(0)
+    d.a_exact, d.b_exact, d.alpha = int(a_exact), int(b_exact), float(alpha)
+    if row_bias is not None:
+        if row_bias.dtype != torch.float32 or row_bias.numel() < M or not row_bias.is_contiguous():
+            raise ValueError("row_bias must be a contiguous float32 tensor with at least M elements")
+        d.row_bias, d.row_bias_scale = row_bias.data_ptr(), float(row_bias_scale)
     lib = _lib.load()
     need = lib.rtdc_gemm_scratch_bytes(C.byref(d))
     if need:
@@ -104,13 +113,15 @@ def gemm_plan(M: int, N: int, K: int, *, b_mn: bool = False, precision: int = PR
 # Linear-layer shaped helpers
 
 def linear_forward(x, weight, bias=None, *, relu=False, drop_p=0.0, seed=0, step=0, step_tensor=None, salt=0,
-                   out=None, n_store=None, precision=PRECISION_FP32, stream=None):
-    """``y = dropout(relu(x @ weight.T + bias))`` in one kernel (K1-K3, K12)."""
+                   out=None, n_store=None, precision=PRECISION_FP32, x_exact=False, alpha=1.0, stream=None):
+    """``y = dropout(relu(alpha * (x @ weight.T) + bias))`` in one kernel (K1-K3, K12). ``x_exact``: the values of
+    ``x`` are exact in tf32 (raw pixels), see :func:`gemm`."""
     B, N = x.shape[0], weight.shape[0]
     if out is None:
         out = torch.empty(B, n_store or N, dtype=torch.float32, device=x.device)
     return gemm(x, weight, out, M=B, N=N, K=weight.shape[1], bias=bias, relu=relu, drop_p=drop_p, seed=seed, step=step,
-                step_tensor=step_tensor, salt=salt, n_store=n_store, precision=precision, stream=stream)
+                step_tensor=step_tensor, salt=salt, n_store=n_store, precision=precision, a_exact=x_exact, alpha=alpha,
+                stream=stream)
 
 
 def linear_dgrad(dy, weight, *, N_out=None, mask_src=None, mask_scale=1.0, out=None, precision=PRECISION_FP32,
@@ -125,11 +136,14 @@ def linear_dgrad(dy, weight, *, N_out=None, mask_src=None, mask_scale=1.0, out=N
                 precision=precision, colsum_partial=colsum_partial, stream=stream)
 
 
-def linear_wgrad(dy, x, *, N_out=None, out=None, precision=PRECISION_FP32, splits=0, stream=None):
-    """``dW[N_out, K_in] = dy[:, :N_out].T @ x`` with split-K over the batch (K6 wgrad). ``out`` may
-    be a view into a gradient bucket, so the gradient is produced in place for the all-reduce."""
+def linear_wgrad(dy, x, *, N_out=None, out=None, precision=PRECISION_FP32, splits=0, x_exact=False, alpha=1.0,
+                 row_bias=None, row_bias_scale=1.0, stream=None):
+    """``dW[N_out, K_in] = alpha * (dy[:, :N_out].T @ x) + row_bias[:, None] * row_bias_scale`` with split-K over the
+    batch (K6 wgrad). ``out`` may be a view into a gradient bucket, so the gradient is produced in place for the
+    all-reduce."""
     n_out = dy.shape[1] if N_out is None else N_out
     B, K_in = x.shape
     if out is None:
         out = torch.empty(n_out, K_in, dtype=torch.float32, device=x.device)
-    return gemm(dy, x, out, a_mn=True, b_mn=True, M=n_out, N=K_in, K=B, precision=precision, splits=splits, stream=stream)
+    return gemm(dy, x, out, a_mn=True, b_mn=True, M=n_out, N=K_in, K=B, precision=precision, splits=splits,
+                b_exact=x_exact, alpha=alpha, row_bias=row_bias, row_bias_scale=row_bias_scale, stream=stream)

@@ -32,7 +32,7 @@ class MLPTrainEngine:
     def __init__(self, model: Optional[NeuralNetwork] = None, *, batch_size: int, lr: float = 1e-3, momentum: float = 0.9,
                  weight_decay: float = 0.0, device=None, seed: int = 0x5EED, precision: int = ops.PRECISION_FP32,
                  use_graph: bool = True, process_group=None, distributed: Optional[bool] = None, algo: str = "auto",
-                 input_mean: float = 0.5, input_std: float = 0.5, fused_head: bool = True):
+                 input_mean: float = 0.5, input_std: float = 0.5, fused_head: bool = True, fold_input: bool = True):
         self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
         if self.device.type == "cuda" and self.device.index is None:
             self.device = torch.device("cuda", torch.cuda.current_device())
@@ -53,6 +53,10 @@ class MLPTrainEngine:
             raise ValueError(f"at most {_LOGIT_LD} classes")
         self.seed, self.precision = seed, precision
         self.mean, self.std = input_mean, input_std
+        # uint8 batches: the normalisation x = s*pixel + t is folded into layer 1 (raw pixels are exact in tf32, so
+        # the two K = 784 GEMMs drop one of their three 3xTF32 passes; see include/rtdc_b200.h, rtdc_gemm_desc.a_exact)
+        self.fold_input = bool(fold_input) and precision == ops.PRECISION_FP32
+        self.in_scale, self.in_shift = 1.0 / (255.0 * input_std), -input_mean / input_std
         self.world = dist.get_world_size(process_group) if (dist.is_initialized() and distributed is not False) else 1
         self.rank = dist.get_rank(process_group) if self.world > 1 else 0
         self.group = process_group
@@ -101,6 +105,7 @@ class MLPTrainEngine:
         self.dh2 = torch.empty(B, self.d_h, device=dev)
         self.dh1 = torch.empty(B, self.d_h, device=dev)
         self.dh1_colsum = torch.zeros(4 * ((B + 127) // 128), self.d_h, device=dev)
+        self.b1_eff = torch.zeros(self.d_h, device=dev)      # b1 + t*rowsum(W1) for the folded input layer
         self.loss = torch.zeros((), device=dev)
         self.step_counter = torch.zeros(1, dtype=torch.int32, device=dev)
         self.eval_loss_sum = torch.zeros((), device=dev)
@@ -146,9 +151,15 @@ class MLPTrainEngine:
         n = 0
         p = self.p_drop if train else 0.0
         kw = dict(seed=self.seed, step_tensor=self.step_counter, precision=self.precision, stream=s)
-        if from_u8:
-            ops.u8_normalize(self.x_u8, mean=self.mean, std=self.std, out=self.x, stream=s); n += 1
-        ops.linear_forward(self.x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, **kw); n += 1
+        if from_u8 and self.fold_input:
+            ops.u8_affine(self.x_u8, out=self.x, stream=s); n += 1                       # raw pixels, exact in tf32
+            ops.fold_input_bias(self.W[0], self.b[0], self.in_shift, out=self.b1_eff, stream=s); n += 1
+            ops.linear_forward(self.x, self.W[0], self.b1_eff, relu=True, drop_p=p, salt=1, out=self.h1, x_exact=True,
+                               alpha=self.in_scale, **kw); n += 1
+        else:
+            if from_u8:
+                ops.u8_normalize(self.x_u8, mean=self.mean, std=self.std, out=self.x, stream=s); n += 1
+            ops.linear_forward(self.x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, **kw); n += 1
         ops.linear_forward(self.h1, self.W[1], self.b[1], relu=True, drop_p=p, salt=2, out=self.h2, **kw); n += 1
         if with_logits:
             ops.linear_forward(self.h2, self.W[2], self.b[2], relu=True, out=self.z, n_store=_LOGIT_LD, **kw); n += 1
@@ -179,9 +190,13 @@ class MLPTrainEngine:
         # dgrad2 also leaves per-32-row column sums of dh1 (592 x 512 instead of 18944 x 512 to sum for db1)
         ops.linear_dgrad(self.dh2, self.W[1], mask_src=self.h1, mask_scale=inv_keep, out=self.dh1, precision=prec,
                          colsum_partial=self.dh1_colsum, stream=s); n += 1
-        # layer 1 (its input needs no gradient)
-        ops.linear_wgrad(self.dh1, self.x, out=self.dW[0], precision=prec, stream=s); n += 2
+        # layer 1 (its input needs no gradient); with folded input dW1 = s*(dh1^T raw) + t*db1 1^T
         ops.colsum(self.dh1_colsum, out=self.db[0], stream=s); n += 1
+        if from_u8 and self.fold_input:
+            ops.linear_wgrad(self.dh1, self.x, out=self.dW[0], precision=prec, x_exact=True, alpha=self.in_scale,
+                             row_bias=self.db[0], row_bias_scale=self.in_shift, stream=s); n += 2
+        else:
+            ops.linear_wgrad(self.dh1, self.x, out=self.dW[0], precision=prec, stream=s); n += 2
         for b in range(len(self.buckets)):
             if b not in launched:
                 self._reduce_bucket(b, s); n += self.world > 1

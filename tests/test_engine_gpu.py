@@ -94,10 +94,21 @@ def test_engine_eval_u8_and_state_roundtrip():
     l2 = e2.step(xu8, y).item()
     l3 = e3.step(xf, y).item()
     assert abs(l2 - l3) < 1e-5
+    # ... including the folded input layer's gradients (dW1 = s*(dh1^T raw) + t*db1 1^T)
+    # (a ReLU unit at ~0 may flip between the two roundings and move one sample's contribution, so the norm bound
+    # is loose and the median, which such outliers cannot move, is tight)
+    for got, ref in zip(e2.dW + e2.db, e3.dW + e3.db):
+        err = (got - ref).abs()
+        assert err.norm() <= 1e-2 * ref.norm()
+        assert err.median() <= 1e-5 * ref.abs().mean()
+    e4 = MLPTrainEngine(NeuralNetwork(), batch_size=B, device="cuda", distributed=False, seed=7, fold_input=False)
+    e4.load_model_state_dict(e3.model_state_dict())
+    e2.step(xu8, y); e3.step(xf, y)
+    assert e2.fold_input and not e4.fold_input
     # checkpoint-format round trip through a bare module
     fresh = e2.copy_to_module(NeuralNetwork())
     assert list(fresh.state_dict()) == list(e2.model_state_dict(prefix=""))
     e3.load_optimizer_state_dict(e2.optimizer_state_dict())
     assert torch.equal(e3.m_arena, e2.m_arena)
-    for e in (eng, e2, e3):
+    for e in (eng, e2, e3, e4):
         e.close()

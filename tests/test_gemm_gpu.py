@@ -127,15 +127,86 @@ def test_plan_and_errors():
         ops.linear_forward(x, w)
 
 
-def test_dgrad_fused_column_sums():
+@pytest.mark.parametrize("B", [1000, 384, 640])
+def test_dgrad_fused_column_sums(B):
+    """1000 rows: 8 tiles of 128 (4 CTA pairs); 384 / 640: an odd number of 128-row tiles, so the last CTA pair's
+    second half lies past M and must not write its (empty) partial rows beyond the buffer."""
     ops = _ops()
-    B, n_out, k_in = 1000, 512, 512
+    n_out, k_in = 512, 512
     g = torch.Generator(device="cuda").manual_seed(8)
     dy = torch.randn(B, n_out, device="cuda", generator=g)
     w = torch.randn(n_out, k_in, device="cuda", generator=g) * 0.05
     h = torch.relu(torch.randn(B, k_in, device="cuda", generator=g))
-    part = torch.full((4 * ((B + 127) // 128), k_in), 7.0, device="cuda")
+    rows = 4 * ((B + 127) // 128)
+    arena = torch.full((rows + 8, k_in), 7.0, device="cuda")
+    part = arena[:rows]
     dx = ops.linear_dgrad(dy, w, mask_src=h, mask_scale=4 / 3, colsum_partial=part)
     groups = (B + 31) // 32
     assert torch.allclose(part[:groups].sum(0).double(), dx.double().sum(0), rtol=1e-4, atol=1e-3)
     assert torch.allclose(ops.colsum(part[:groups].contiguous()).double(), dx.double().sum(0), rtol=1e-4, atol=1e-3)
+    assert bool((arena[rows:] == 7.0).all()), "partial sums written past the buffer"
+
+
+@pytest.mark.parametrize("which", ["a", "b", "both"])
+def test_exact_operand_and_affine_epilogue(which):
+    """Operands whose values are exact in tf32 (raw pixels) skip their correction pass; alpha / row_bias fold an input
+    normalisation into the layer. fp32-accurate against float64."""
+    from ray_torch_distributed_checkpoint_b200 import ops
+    torch.manual_seed(3)
+    M, N, K = 300, 520, 784
+    s, t = 2.0 / 255.0, -1.0
+    ints = lambda *shape: torch.randint(0, 256, shape, device="cuda").float()
+    a = ints(M, K) if which in ("a", "both") else torch.randn(M, K, device="cuda")
+    b = ints(N, K) if which in ("b", "both") else torch.randn(N, K, device="cuda") * 0.05
+    bias = torch.randn(N, device="cuda")
+    rb = torch.randn(M, device="cuda")
+    ref = s * (a.double() @ b.double().T) + bias.double() + t * rb.double()[:, None]
+    scale = (s * (a.double().abs() @ b.double().abs().T)).max().item()
+    for splits in (1, 0):      # in-kernel epilogue, then the split-K reduce epilogue
+        out = torch.empty(M, N, device="cuda")
+        ops.gemm(a, b, out, bias=bias, relu=False, a_exact=which in ("a", "both"), b_exact=which in ("b", "both"), alpha=s,
+                 row_bias=rb, row_bias_scale=t, splits=splits)
+        assert (out.double() - ref).abs().max().item() < 1.2e-5 * scale, splits
+    # the same through split-K (wgrad shape: both operands MN-major, K = batch)
+    Kb = 4096
+    dy = torch.randn(Kb, 64, device="cuda")
+    x = ints(Kb, 200)
+    db = dy.sum(0)
+    dw = torch.empty(64, 200, device="cuda")
+    ops.linear_wgrad(dy, x, out=dw, x_exact=True, alpha=s, row_bias=db, row_bias_scale=t)
+    ref = dy.double().T @ (s * x.double() + t)
+    scale = (dy.double().abs().T @ (s * x.double())).max().item()
+    assert (dw.double() - ref).abs().max().item() < 1.2e-5 * scale
+    assert ops.gemm_plan(64, 200, Kb, b_mn=True)["splits"] > 1
+
+
+def test_fold_input_bias():
+    from ray_torch_distributed_checkpoint_b200 import ops
+    torch.manual_seed(4)
+    for rows, cols in ((512, 784), (7, 33), (64, 1000)):
+        w = torch.randn(rows, cols, device="cuda")
+        b = torch.randn(rows, device="cuda")
+        got = ops.fold_input_bias(w, b, -1.0)
+        ref = b.double() - w.double().sum(1)
+        assert (got.double() - ref).abs().max().item() < 1e-4
+        assert torch.equal(ops.fold_input_bias(w, None, 0.5), ops.fold_input_bias(w, None, 0.5))
+
+
+def test_u8_affine_widens_exactly():
+    from ray_torch_distributed_checkpoint_b200 import ops
+    src = torch.arange(256, dtype=torch.uint8, device="cuda").repeat(64)
+    assert torch.equal(ops.u8_affine(src), src.float())
+
+
+@pytest.mark.parametrize("bn", [0, 176, 48])
+def test_multi_tile_n_not_multiple_of_32(bn):
+    """Several N tiles whose width is not a multiple of the 32-column store box (regression: the last box of a tile
+    used to overwrite the first columns of the next tile)."""
+    from ray_torch_distributed_checkpoint_b200 import ops
+    torch.manual_seed(5)
+    M, N, K = 300, 520, 96
+    a, b = torch.randn(M, K, device="cuda"), torch.randn(N, K, device="cuda")
+    out = torch.full((M, N), float("nan"), device="cuda")
+    ops.gemm(a, b, out, bn=bn, splits=1)
+    ref = a.double() @ b.double().T
+    assert (out.double() - ref).abs().max().item() < 4e-6 * (a.double().abs() @ b.double().abs().T).max().item()

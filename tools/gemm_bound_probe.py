@@ -1,0 +1,33 @@
+"""Which stage bounds the 3xTF32 main loop? fwd1 shape, RTDC_GEMM_DEBUG bits (1 no TMA, 2 no MMA, 4 no stores,
+8 no split) x exact-A x bn."""
+import os, sys
+import torch
+from ray_torch_distributed_checkpoint_b200 import ops
+B = 18944
+dev = "cuda"
+x = torch.randint(0, 256, (B, 784), device=dev).float(); w1 = torch.randn(512, 784, device=dev) * .03; b1 = torch.randn(512, device=dev)
+out = torch.empty(B, 512, device=dev)
+def t(fn, n=10):
+    for _ in range(3): fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            for _ in range(n): fn()
+        g.replay(); s.synchronize()
+        a.record(s); g.replay(); b.record(s); s.synchronize()
+    return a.elapsed_time(b) / n * 1000
+for bn in (256, 128):
+    for ex in (False, True):
+        row = []
+        for dbg in (0, 8, 2, 10, 1, 9, 3, 11):
+            os.environ["RTDC_GEMM_DEBUG"] = str(dbg)
+            us = t(lambda: ops.gemm(x, w1, out, bias=b1, relu=True, precision=3, a_exact=ex, bn=bn))
+            row.append(f"dbg{dbg}={us:.1f}")
+        print(f"bn={bn} a_exact={int(ex)} stages={ops.gemm_plan(B, 512, 784, bn=bn)['stages']}: " + " ".join(row), flush=True)
+os.environ["RTDC_GEMM_DEBUG"] = "0"
+for bn in (256, 128):
+    us = t(lambda: ops.gemm(x, w1, out, bias=b1, relu=True, precision=1, bn=bn))
+    print(f"tf32 1-pass BK=32 bn={bn}: {us:.1f} us")
