@@ -68,12 +68,14 @@ __device__ __forceinline__ uint32_t rand16(const Philox4& r, int j) {
 
 // Epilogue of one work unit, run by the four epilogue warps: TMEM -> registers -> (+bias, ReLU, dropout,
 // backward mask) -> swizzled smem box -> TMA store (or split-K partial to scratch). `release()` hands the
-// accumulator buffer back to the MMA issuer right after this warp's last TMEM read.
+// accumulator buffer back to the MMA issuer right after this warp's last TMEM read. `part` selects the 32-column
+// chunks this call covers: 0 = all, 1 = first half, 2 = second half (the CTA's final unit is shared with the splitter
+// warps, which have nothing left to split by then).
 template <class ReleaseFn>
 __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtensorMap* tmOut, uint32_t taddr, int umma_n,
                                               int tile, int split, int m0, int n0, int r_in_tile, int lane, int wq,
                                               const float* s_bias, uint8_t* stage_buf, uint32_t& stores_issued,
-                                              uint32_t step, ReleaseFn release) {
+                                              uint32_t step, ReleaseFn release, int part = 0) {
   const bool has_drop = p.drop_thr16 != 0u;
   const bool has_mask = p.mask_src != nullptr;
   const bool relu = p.relu != 0;
@@ -88,7 +90,8 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
     // split-K: park this split's partial tile in scratch; splitk_reduce_kernel sums the splits in
     // order (deterministic) and applies the epilogue
     float* my = p.scratch + (static_cast<size_t>(tile < 0 ? 0 : tile) * p.splits + split) * (BM * MAX_BN);
-    for (int c = 0; c < (tile < 0 ? 0 : acc_chunks); ++c) {
+    const int total = tile < 0 ? 0 : acc_chunks, half = (total + 1) >> 1;
+    for (int c = (part == 2 ? half : 0); c < (part == 1 ? half : total); ++c) {
       tmem_ld_32x32(taddr + c * 32, r);
       tmem_ld_wait();
       float4* dst = reinterpret_cast<float4*>(my + (static_cast<size_t>(c) * BM + r_in_tile) * 32);
@@ -103,7 +106,18 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
     return;
   }
 
-  for (int c = 0; c < n_chunks; ++c) {
+  // backward mask of chunk 0 (the loads of chunk c+1 are issued while chunk c is being processed)
+  const bool mask_vec_ok = has_mask && row < p.M && ((reinterpret_cast<uintptr_t>(p.mask_src) & 15u) == 0) && (p.ldm & 3) == 0 &&
+                           (n0 & 3) == 0;
+  const int c_half = (n_chunks + 1) >> 1;
+  const int c_begin = part == 2 ? c_half : 0, c_end = part == 1 ? c_half : n_chunks;
+  float4 mk[8];
+  if (mask_vec_ok && c_begin < c_end && n0 + c_begin * 32 + 32 <= p.N) {
+    const float4* ms4 = reinterpret_cast<const float4*>(p.mask_src + static_cast<size_t>(row) * p.ldm + n0 + c_begin * 32);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) mk[q] = __ldg(ms4 + q);
+  }
+  for (int c = c_begin; c < c_end; ++c) {
     float v[32];
     if (c < acc_chunks) {
       tmem_ld_32x32(taddr + c * 32, r);
@@ -115,15 +129,34 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
       __syncwarp();
       release();
     }
-#pragma unroll
-    for (int q = 0; q < 32; ++q) v[q] = (c < acc_chunks) ? __uint_as_float(r[q]) : 0.f;
     // TMEM columns past the MMA's N were never written: force them (and their bias) to zero.
     // Columns between N and umma_n hold exact zeros already (TMA zero-fills out-of-range B rows).
     const int live = umma_n - c * 32;
+    if (live >= 32) {
+      // whole chunk live: bias through eight 128-bit shared loads (independent of one another; the element-wise
+      // form below compiles to a serial chain of predicated scalar loads)
+      float4 bb[8];
 #pragma unroll
-    for (int q = 0; q < 32; ++q) {
-      float x = (q < live) ? fmaf(v[q], alpha, s_bias[c * 32 + q]) + rb : 0.f;
-      v[q] = relu ? fmaxf(x, 0.f) : x;
+      for (int q = 0; q < 8; ++q) bb[q] = reinterpret_cast<const float4*>(s_bias + c * 32)[q];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float x0 = fmaf(__uint_as_float(r[4 * q]), alpha, bb[q].x) + rb;
+        const float x1 = fmaf(__uint_as_float(r[4 * q + 1]), alpha, bb[q].y) + rb;
+        const float x2 = fmaf(__uint_as_float(r[4 * q + 2]), alpha, bb[q].z) + rb;
+        const float x3 = fmaf(__uint_as_float(r[4 * q + 3]), alpha, bb[q].w) + rb;
+        v[4 * q] = relu ? fmaxf(x0, 0.f) : x0;
+        v[4 * q + 1] = relu ? fmaxf(x1, 0.f) : x1;
+        v[4 * q + 2] = relu ? fmaxf(x2, 0.f) : x2;
+        v[4 * q + 3] = relu ? fmaxf(x3, 0.f) : x3;
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < 32; ++q) v[q] = (c < acc_chunks) ? __uint_as_float(r[q]) : 0.f;
+#pragma unroll
+      for (int q = 0; q < 32; ++q) {
+        float x = (q < live) ? fmaf(v[q], alpha, s_bias[c * 32 + q]) + rb : 0.f;
+        v[q] = relu ? fmaxf(x, 0.f) : x;
+      }
     }
     const int col0 = n0 + c * 32;
     // dropout: element index e = row*N + col, 8 elements per Philox call, 16 bits each
@@ -155,10 +188,7 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
     // backward mask of the previous layer's ReLU+dropout output
     if (has_mask && row < p.M) {
       const float* ms = p.mask_src + static_cast<size_t>(row) * p.ldm + col0;
-      if (col0 + 32 <= p.N && ((reinterpret_cast<uintptr_t>(ms) & 15u) == 0)) {
-        float4 mk[8];
-#pragma unroll
-        for (int q = 0; q < 8; ++q) mk[q] = __ldg(reinterpret_cast<const float4*>(ms) + q);
+      if (mask_vec_ok && col0 + 32 <= p.N) {
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
           v[4 * q] = mk[q].x > 0.f ? v[4 * q] * p.mask_scale : 0.f;
@@ -170,6 +200,11 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
 #pragma unroll
         for (int q = 0; q < 32; ++q)
           if (col0 + q < p.N) v[q] = (__ldg(ms + q) > 0.f) ? v[q] * p.mask_scale : 0.f;
+      }
+      // next chunk's mask: in flight during this chunk's stores and the next TMEM load
+      if (mask_vec_ok && c + 1 < c_end && col0 + 64 <= p.N) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) mk[q] = __ldg(reinterpret_cast<const float4*>(ms + 32) + q);
       }
     }
     if (p.debug & 4) continue;
@@ -229,7 +264,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __shared__ __align__(8) uint64_t tmem_full_bar[2];    // MMA -> epilogue: accumulator buffer complete
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];   // epilogue -> MMA: accumulator buffer drained
   __shared__ uint32_t tmem_base_slot;
-  __shared__ float s_bias[MAX_BN];
+  __shared__ __align__(16) float s_bias[MAX_BN];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -273,6 +308,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // the epilogue of unit j overlaps the main loop of unit j+1.
   const int tiles = p.m_tiles * p.n_tiles;
   const int total_units = tiles * p.splits;
+  // the splitter warps help with the CTA's final epilogue when the ring can host their four store boxes
+  const bool share_final = !(p.debug & 32) && static_cast<uint32_t>(p.stages) * p.stage_bytes >= 32768u;
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -429,6 +466,27 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
     }
+    // nothing left to split: take the second half of this CTA's final epilogue (staging boxes in the idle ring)
+    if (share_final) {
+      const int n_mine = (total_units - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+      const int j = n_mine - 1, u = static_cast<int>(blockIdx.x) + j * static_cast<int>(gridDim.x);
+      const int tile = u % tiles, split = u / tiles;
+      const int m0 = (tile % p.m_tiles) * BM, n0 = (tile / p.m_tiles) * p.bn;
+      const int n_valid = min(p.bn, p.N - n0);
+      const int umma_n = min(p.bn, (n_valid + 15) & ~15);
+      const int buf = j & 1;
+      const int wq = warp & 3;
+      const uint32_t taddr = tmem_base + static_cast<uint32_t>(buf) * MAX_BN + (static_cast<uint32_t>(wq * 32) << 16);
+      uint32_t step = p.step_imm;
+      if (p.drop_thr16 != 0u && p.step_ptr != nullptr) step = *p.step_ptr;
+      uint32_t stores_issued = 0;
+      named_bar_sync(2, SPLIT_THREADS + EPI_THREADS);   // the epilogue warps have staged this unit's bias slice
+      mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);     // all MMAs done: accumulators complete, ring idle
+      tcgen05_fence_after();
+      epilogue_unit(p, &tmOut, taddr, umma_n, tile, split, m0, n0, wq * 32 + lane, lane, wq, s_bias, ring_ptr + static_cast<size_t>(wq) * 8192,
+                    stores_issued, step, []() {}, 2);
+      if (p.tma_store && lane == 0) tma_store_wait_all();
+    }
   } else {
     // ------------------------------------------------------------------ epilogue warps
     const int et = threadIdx.x - (64 + SPLIT_THREADS);  // 0..127
@@ -448,16 +506,17 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t taddr = tmem_base + static_cast<uint32_t>(buf) * MAX_BN + (static_cast<uint32_t>(wq * 32) << 16);
 
       // bias slice of this tile -> smem (zero beyond N); the barrier also fences the previous unit's reads
+      const bool shared = share_final && u + static_cast<int>(gridDim.x) >= total_units;   // final unit: split with the splitter warps
       named_bar_sync(1, EPI_THREADS);
       for (int c = et; c < MAX_BN; c += EPI_THREADS)
         s_bias[c] = (p.bias != nullptr && c < p.bn && n0 + c < p.N) ? __ldg(p.bias + n0 + c) : 0.f;
-      named_bar_sync(1, EPI_THREADS);
+      if (shared) named_bar_sync(2, SPLIT_THREADS + EPI_THREADS); else named_bar_sync(1, EPI_THREADS);
 
       mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);
       tcgen05_fence_after();
 
       epilogue_unit(p, &tmOut, taddr, umma_n, tile, split, m0, n0, r_in_tile, lane, wq, s_bias, stage_buf, stores_issued, step,
-                    [&]() { if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]); });
+                    [&]() { if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]); }, shared ? 1 : 0);
     }
     if (p.tma_store && lane == 0) tma_store_wait_all();  // smem must outlive the bulk reads
   }
@@ -492,7 +551,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
   __shared__ __align__(8) uint64_t tmem_full_bar[2];
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_slot;
-  __shared__ float s_bias[MAX_BN];
+  __shared__ __align__(16) float s_bias[MAX_BN];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -535,6 +594,11 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
   const int tiles2 = p.m_tiles2 * p.n_tiles;
   const int total_units = tiles2 * p.splits;
   const int half_bn = p.bn >> 1;
+  // RTDC_GEMM_DEBUG_BUF: per-CTA stamps [grid][16]: 0 start clk, 1/2 first-unit epilogue begin/end, 3/4 last-unit epilogue
+  // begin/end, 5 end clk, 6/7 end/start ns, 8/9 issuer: first/last unit's MMAs issued
+  const bool share_final = !(p.debug & 32) && static_cast<uint32_t>(p.stages) * p.stage_bytes >= 32768u;
+  long long* stamps = p.dbg_times ? p.dbg_times + static_cast<size_t>(blockIdx.x) * 16 : nullptr;
+  if (stamps && threadIdx.x == 0) { stamps[0] = clock64(); stamps[7] = static_cast<long long>(global_timer_ns()); }
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (both CTAs)
@@ -626,6 +690,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
           if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
         tcgen05_commit_2cta(&tmem_full_bar[buf], 0x3);    // both halves of the accumulator are complete
+        if (stamps) { if (j == 0) stamps[8] = clock64(); stamps[9] = clock64(); }
       }
     }
     __syncwarp();
@@ -671,6 +736,30 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
         if (++s == p.stages) { s = 0; ph ^= 1u; }
       }
     }
+    // nothing left to split: take the second half of this CTA's final epilogue (staging boxes in the idle ring)
+    if (share_final) {
+      const int n_mine = (total_units - pair + num_pairs - 1) / num_pairs;
+      const int j = n_mine - 1, u = pair + j * num_pairs;
+      const int tile2 = u % tiles2, split = u / tiles2;
+      const int m_tile128 = (tile2 % p.m_tiles2) * 2 + static_cast<int>(rank);
+      const int n_tile = tile2 / p.m_tiles2;
+      const int m0 = m_tile128 * BM, n0 = n_tile * p.bn;
+      const int gran2 = B_MN ? 64 : 32;
+      const int umma_n = min(p.bn, (min(p.bn, p.N - n0) + gran2 - 1) / gran2 * gran2);
+      const int tile128 = m_tile128 < p.m_tiles ? n_tile * p.m_tiles + m_tile128 : -1;
+      const int buf = j & 1;
+      const int wq = warp & 3;
+      const uint32_t taddr = tmem_base + static_cast<uint32_t>(buf) * MAX_BN + (static_cast<uint32_t>(wq * 32) << 16);
+      uint32_t step = p.step_imm;
+      if (p.drop_thr16 != 0u && p.step_ptr != nullptr) step = *p.step_ptr;
+      uint32_t stores_issued = 0;
+      named_bar_sync(2, SPLIT_THREADS + EPI_THREADS);   // the epilogue warps have staged this unit's bias slice
+      mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);     // the pair's MMAs are done: accumulators complete, both rings idle
+      tcgen05_fence_after();
+      epilogue_unit(p, &tmOut, taddr, umma_n, tile128, split, m0, n0, wq * 32 + lane, lane, wq, s_bias,
+                    ring_ptr + static_cast<size_t>(wq) * 8192, stores_issued, step, []() {}, 2);
+      if (p.tma_store && lane == 0) tma_store_wait_all();
+    }
   } else {
     // ------------------------------------------------------------------ epilogue warps (both CTAs, own 128 rows)
     const int et = threadIdx.x - (64 + SPLIT_THREADS);
@@ -691,14 +780,17 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       const int tile128 = m_tile128 < p.m_tiles ? n_tile * p.m_tiles + m_tile128 : -1;   // -1: rows entirely past M
       const int buf = j & 1;
       const uint32_t taddr = tmem_base + static_cast<uint32_t>(buf) * MAX_BN + (static_cast<uint32_t>(wq * 32) << 16);
+      const bool shared = share_final && u + num_pairs >= total_units;   // final unit: split with the splitter warps
       named_bar_sync(1, EPI_THREADS);
       for (int c = et; c < MAX_BN; c += EPI_THREADS)
         s_bias[c] = (p.bias != nullptr && c < p.bn && n0 + c < p.N) ? __ldg(p.bias + n0 + c) : 0.f;
-      named_bar_sync(1, EPI_THREADS);
+      if (shared) named_bar_sync(2, SPLIT_THREADS + EPI_THREADS); else named_bar_sync(1, EPI_THREADS);
       mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);
       tcgen05_fence_after();
+      if (stamps && et == 0) { if (j == 0) stamps[1] = clock64(); stamps[3] = clock64(); }
       epilogue_unit(p, &tmOut, taddr, umma_n, tile128, split, m0, n0, r_in_tile, lane, wq, s_bias, stage_buf, stores_issued, step,
-                    [&]() { if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[buf], 0); });
+                    [&]() { if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[buf], 0); }, shared ? 1 : 0);
+      if (stamps && et == 0) { if (j == 0) stamps[2] = clock64(); stamps[4] = clock64(); }
     }
     if (p.tma_store && lane == 0) tma_store_wait_all();
   }
@@ -706,6 +798,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
   // teardown: nobody may leave (or free TMEM) while the peer can still read this CTA's smem / arrive here
   tcgen05_fence_before();
   __syncthreads();
+  if (stamps && threadIdx.x == 0) { stamps[5] = clock64(); stamps[6] = static_cast<long long>(global_timer_ns()); }
   cluster_sync_all();
   if (warp == 1) tmem_dealloc_2cta(tmem_base, TMEM_COLS);
 }
