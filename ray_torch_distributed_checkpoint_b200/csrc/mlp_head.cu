@@ -6,7 +6,7 @@
 // Why a dedicated kernel: with 10 output classes these ops are 1.3 % of the step's FLOPs but, run as
 // three skinny tensor-core GEMMs + a loss kernel + reductions, they were 16 % of its time — each of them
 // re-reads the 39 MB activation matrix and pays a full pipeline prologue for almost no math. Here a
-// block loads a 64-row tile of H once into shared memory and produces, in exact fp32 FFMA arithmetic:
+// block loads a 32-row tile of H once into shared memory and produces, in exact fp32 FFMA arithmetic:
 //   z = relu(H W^T + b)            (never written out)
 //   loss_i, dz = (softmax(z) - onehot) * grad_scale * 1[z > 0]
 //   dH = (dz W) * 1[H > 0] * mask_scale      -> global (the only large write)
@@ -16,9 +16,13 @@
 
 namespace rtdc {
 
-constexpr int HD_ROWS = 64;       // rows of H per tile
-constexpr int HD_THREADS = 512;     // 16 warps: one block per SM (157 KB of smem), so latency hiding has to come from warps
-constexpr int HD_MAXK = 512;      // hidden width limit (smem tile 64 x 512 fp32 = 128 KB)
+// Two blocks per SM (89 KB of smem each at K = 512): while one block waits for its H tile to land, the other computes,
+// so the tile load needs no double buffering inside a block.
+constexpr int HD_ROWS = 32;       // rows of H per tile
+constexpr int HD_THREADS = 256;     // 8 warps per block, 2 blocks per SM
+constexpr int HD_GROUPS = HD_THREADS / 128;   // thread groups of 128 (one float4 column slice per thread) in phases C/D
+constexpr int HD_BLOCKS_PER_SM = 2;
+constexpr int HD_MAXK = 512;      // hidden width limit (smem tile 32 x 512 fp32 = 64 KB)
 constexpr int HD_PAD = 4;         // row padding (floats) -> conflict-free 128-bit accesses across rows
 constexpr int HD_DZ_LD = 16;      // dz rows padded to 16 floats
 
@@ -37,7 +41,7 @@ struct HeadParams {
 };
 
 template <int C>
-__global__ void __launch_bounds__(HD_THREADS, 1)
+__global__ void __launch_bounds__(HD_THREADS, HD_BLOCKS_PER_SM)
 mlp_head_train_kernel(const HeadParams p) {
   extern __shared__ __align__(16) float smem[];
   const int K = p.K, K4 = K >> 2, LD = K + HD_PAD;
@@ -56,7 +60,7 @@ mlp_head_train_kernel(const HeadParams p) {
   if (t < 16) sb[t] = (t < C && p.bias != nullptr) ? __ldg(p.bias + t) : 0.f;
 
   // persistent accumulators
-  constexpr int CH = (C + 3) / 4;          // classes per thread group in the dW phase (four groups)
+  constexpr int CH = (C + HD_GROUPS - 1) / HD_GROUPS;   // classes per thread group in the dW phase
   float4 dw_acc[CH];
 #pragma unroll
   for (int c = 0; c < CH; ++c) dw_acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -88,12 +92,13 @@ mlp_head_train_kernel(const HeadParams p) {
 
     // ---- B: logits for two rows per thread (16 threads share a row pair and stride over K), then CE
     {
-      const int g = t & 15, rp = t >> 4;   // rp in 0..31: rows rp and rp + 32
+      const int g = t & 15, rp = t >> 4;   // rp in 0..HD_ROWS/2-1: rows rp and rp + HD_ROWS/2
+      static_assert(HD_THREADS / 16 == HD_ROWS / 2, "phase B maps 16 threads to a pair of rows");
       float a0[C], a1[C];
 #pragma unroll
       for (int c = 0; c < C; ++c) { a0[c] = 0.f; a1[c] = 0.f; }
       const float* h0 = sh + rp * LD;
-      const float* h1 = sh + (rp + 32) * LD;
+      const float* h1 = sh + (rp + HD_ROWS / 2) * LD;
       for (int k4 = g; k4 < K4; k4 += 16) {
         const float4 x0 = *reinterpret_cast<const float4*>(h0 + 4 * k4);
         const float4 x1 = *reinterpret_cast<const float4*>(h1 + 4 * k4);
@@ -112,8 +117,8 @@ mlp_head_train_kernel(const HeadParams p) {
           a1[c] += __shfl_xor_sync(0xffffffffu, a1[c], o);
         }
       }
-      if (g < 2) {                         // g == 0 finishes row rp, g == 1 finishes row rp + 32
-        const int r = rp + 32 * g;
+      if (g < 2) {                         // g == 0 finishes row rp, g == 1 finishes row rp + HD_ROWS/2
+        const int r = rp + (HD_ROWS / 2) * g;
         const int row = row0 + r;
         float z[C];
         float mx = -INFINITY;
@@ -154,14 +159,15 @@ mlp_head_train_kernel(const HeadParams p) {
       db_acc += sacc;
     }
 
-    const int k4 = t & 127, grp = t >> 7;  // four groups of 128 threads; thread owns columns 4*k4..4*k4+3
+    const int k4 = t & 127, grp = t >> 7;  // groups of 128 threads; thread owns columns 4*k4..4*k4+3
+    constexpr int RPG = HD_ROWS / HD_GROUPS;   // rows per group in phase C
     if (k4 < K4) {
-      // ---- C: dH = (dz W) masked by H > 0, rows grp*16 .. grp*16+15
+      // ---- C: dH = (dz W) masked by H > 0, rows grp*RPG .. grp*RPG+RPG-1
       {
         float4 wr[C];
 #pragma unroll
         for (int c = 0; c < C; ++c) wr[c] = *reinterpret_cast<const float4*>(sw + c * LD + 4 * k4);
-        for (int r = grp * 16; r < grp * 16 + 16; ++r) {
+        for (int r = grp * RPG; r < grp * RPG + RPG; ++r) {
           const int row = row0 + r;
           if (row >= p.rows) break;
           float d[HD_DZ_LD];
@@ -211,13 +217,13 @@ mlp_head_train_kernel(const HeadParams p) {
       }
     }
     if (p.dbh_partial != nullptr) {
-      __syncthreads();                     // everyone is done with the H tile: reuse it as a [4][K] staging area
+      __syncthreads();                     // everyone is done with the H tile: reuse it as a [groups][K] staging area
       if (k4 < K4) *reinterpret_cast<float4*>(sh + grp * LD + 4 * k4) = dbh_acc;
       __syncthreads();
       if (grp == 0 && k4 < K4) {
         float4 tot = *reinterpret_cast<const float4*>(sh + 4 * k4);
 #pragma unroll
-        for (int g2 = 1; g2 < 4; ++g2) {
+        for (int g2 = 1; g2 < HD_GROUPS; ++g2) {
           const float4 u = *reinterpret_cast<const float4*>(sh + g2 * LD + 4 * k4);
           tot.x += u.x; tot.y += u.y; tot.z += u.z; tot.w += u.w;
         }
@@ -306,7 +312,10 @@ using namespace rtdc;
 
 static int head_grid(int rows) {
   const int tiles = (rows + HD_ROWS - 1) / HD_ROWS;
-  return tiles < 148 ? tiles : 148;
+  int sms = 0, dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+  const int cap = sms * HD_BLOCKS_PER_SM;
+  return tiles < cap ? tiles : cap;
 }
 
 RTDC_API size_t rtdc_mlp_head_scratch_bytes(int rows, int K, int classes) {

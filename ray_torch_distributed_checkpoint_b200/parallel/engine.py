@@ -28,6 +28,14 @@ from . import buckets as _buckets
 _LOGIT_LD = 16          # logits / dlogits rows padded to 16 floats (TMA needs 16-byte row pitch)
 
 
+def _tf32_exact_pixels(shift: float) -> bool:
+    """True when pixel + shift is exactly representable in tf32 (10 explicit mantissa bits) for every uint8 pixel."""
+    import numpy as np
+    v = np.arange(256, dtype=np.float64) + float(shift)
+    f = v.astype(np.float32)
+    return bool((f.astype(np.float64) == v).all() and ((f.view(np.uint32) & 0x1FFF) == 0).all())
+
+
 class MLPTrainEngine:
     def __init__(self, model: Optional[NeuralNetwork] = None, *, batch_size: int, lr: float = 1e-3, momentum: float = 0.9,
                  weight_decay: float = 0.0, device=None, seed: int = 0x5EED, precision: int = ops.PRECISION_FP32,
@@ -53,10 +61,15 @@ class MLPTrainEngine:
             raise ValueError(f"at most {_LOGIT_LD} classes")
         self.seed, self.precision = seed, precision
         self.mean, self.std = input_mean, input_std
-        # uint8 batches: the normalisation x = s*pixel + t is folded into layer 1 (raw pixels are exact in tf32, so
-        # the two K = 784 GEMMs drop one of their three 3xTF32 passes; see include/rtdc_b200.h, rtdc_gemm_desc.a_exact)
-        self.fold_input = bool(fold_input) and precision == ops.PRECISION_FP32
+        # uint8 batches: the normalisation x = s*pixel + t = s*(pixel + t/s) is folded into layer 1. Raw (or shifted) pixels
+        # are exact in tf32, so the two K = 784 GEMMs drop one of their three 3xTF32 passes (include/rtdc_b200.h,
+        # rtdc_gemm_desc.a_exact). "shift": pixel + t/s is itself exact (mean 0.5 -> pixel - 127.5), the layer just scales its
+        # accumulator by s. "fold": otherwise W x + b = s*(W pixel) + (b + t*rowsum(W)), dW = s*(dY^T pixel) + t*db 1^T.
         self.in_scale, self.in_shift = 1.0 / (255.0 * input_std), -input_mean / input_std
+        self.input_mode = "plain"
+        if fold_input and precision == ops.PRECISION_FP32:
+            self.input_mode = "shift" if _tf32_exact_pixels(self.in_shift / self.in_scale) else "fold"
+        self.fold_input = self.input_mode != "plain"
         self.world = dist.get_world_size(process_group) if (dist.is_initialized() and distributed is not False) else 1
         self.rank = dist.get_rank(process_group) if self.world > 1 else 0
         self.group = process_group
@@ -151,7 +164,11 @@ class MLPTrainEngine:
         n = 0
         p = self.p_drop if train else 0.0
         kw = dict(seed=self.seed, step_tensor=self.step_counter, precision=self.precision, stream=s)
-        if from_u8 and self.fold_input:
+        if from_u8 and self.input_mode == "shift":
+            ops.u8_affine(self.x_u8, shift=self.in_shift / self.in_scale, out=self.x, stream=s); n += 1   # pixel - 127.5: exact
+            ops.linear_forward(self.x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, x_exact=True,
+                               alpha=self.in_scale, **kw); n += 1
+        elif from_u8 and self.input_mode == "fold":
             ops.u8_affine(self.x_u8, out=self.x, stream=s); n += 1                       # raw pixels, exact in tf32
             ops.fold_input_bias(self.W[0], self.b[0], self.in_shift, out=self.b1_eff, stream=s); n += 1
             ops.linear_forward(self.x, self.W[0], self.b1_eff, relu=True, drop_p=p, salt=1, out=self.h1, x_exact=True,
@@ -192,7 +209,9 @@ class MLPTrainEngine:
                          colsum_partial=self.dh1_colsum, stream=s); n += 1
         # layer 1 (its input needs no gradient); with folded input dW1 = s*(dh1^T raw) + t*db1 1^T
         ops.colsum(self.dh1_colsum, out=self.db[0], stream=s); n += 1
-        if from_u8 and self.fold_input:
+        if from_u8 and self.input_mode == "shift":
+            ops.linear_wgrad(self.dh1, self.x, out=self.dW[0], precision=prec, x_exact=True, alpha=self.in_scale, stream=s); n += 2
+        elif from_u8 and self.input_mode == "fold":
             ops.linear_wgrad(self.dh1, self.x, out=self.dW[0], precision=prec, x_exact=True, alpha=self.in_scale,
                              row_bias=self.db[0], row_bias_scale=self.in_shift, stream=s); n += 2
         else:

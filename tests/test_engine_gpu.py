@@ -104,11 +104,21 @@ def test_engine_eval_u8_and_state_roundtrip():
     e4 = MLPTrainEngine(NeuralNetwork(), batch_size=B, device="cuda", distributed=False, seed=7, fold_input=False)
     e4.load_model_state_dict(e3.model_state_dict())
     e2.step(xu8, y); e3.step(xf, y)
-    assert e2.fold_input and not e4.fold_input
+    assert e2.input_mode == "shift" and e4.input_mode == "plain"
+    # a normalisation whose shifted pixels are not tf32-exact takes the rowsum-folding route; same step as plain
+    kw = dict(batch_size=B, device="cuda", distributed=False, seed=7, input_mean=0.1307, input_std=0.3081)
+    e5, e6 = MLPTrainEngine(NeuralNetwork(), **kw), MLPTrainEngine(NeuralNetwork(), fold_input=False, **kw)
+    e6.load_model_state_dict(e5.model_state_dict())
+    assert e5.input_mode == "fold" and e6.input_mode == "plain"
+    assert abs(e5.step(xu8, y).item() - e6.step(xu8, y).item()) < 1e-5
+    for got, ref in zip(e5.dW + e5.db, e6.dW + e6.db):
+        err = (got - ref).abs()
+        assert err.norm() <= 1e-2 * ref.norm()
+        assert err.median() <= 1e-5 * ref.abs().mean()
     # checkpoint-format round trip through a bare module
     fresh = e2.copy_to_module(NeuralNetwork())
     assert list(fresh.state_dict()) == list(e2.model_state_dict(prefix=""))
     e3.load_optimizer_state_dict(e2.optimizer_state_dict())
     assert torch.equal(e3.m_arena, e2.m_arena)
-    for e in (eng, e2, e3, e4):
+    for e in (eng, e2, e3, e4, e5, e6):
         e.close()
