@@ -139,7 +139,9 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    # ---- device-timed region
+    # ---- device-timed region. Batch i+1 is staged (device copy + uint8 -> fp32 conversion on the engine's staging
+    # stream) before step i is launched, so the conversion overlaps that step; the timed region holds exactly K
+    # stagings and K steps (the first staging is exposed, the others overlap).
     for i in range(max(W, 3)):
         eng.step(dev_x[i % rot], dev_y[i % rot])
     barrier()
@@ -147,8 +149,11 @@ def run_ours(args):
     with ClockSampler(local) as clk:
         barrier()
         e0.record()
+        eng.stage(dev_x[0], dev_y[0])
         for i in range(K):
-            eng.step(dev_x[i % rot], dev_y[i % rot])
+            if i + 1 < K:
+                eng.stage(dev_x[(i + 1) % rot], dev_y[(i + 1) % rot])
+            eng.step()
         e1.record()
         torch.cuda.synchronize(dev)
         barrier()
@@ -173,9 +178,13 @@ def run_ours(args):
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
     wall0 = time.perf_counter()
     t0.record()
+    xb, yb = next(it)                                         # step 0's H2D (exposed)
+    eng.stage(xb, yb)
     for i in range(K):
-        xb, yb = next(it)                                     # this step's H2D (issued `lookahead` steps ahead)
-        loss = eng.step(xb, yb)
+        if i + 1 < K:
+            xb, yb = next(it)                                 # next step's H2D (issued `lookahead` steps ahead) ...
+            eng.stage(xb, yb)                                 # ... and conversion, overlapping this step
+        loss = eng.step()
         slot = i % 4
         loss_host[slot].copy_(loss, non_blocking=True)        # this step's D2H
         ev = torch.cuda.Event(); ev.record()
@@ -211,7 +220,7 @@ def run_ours(args):
         "clocks": clk.summary(),
         "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "ms_per_step": round(e2e_ms / K, 4),
                 "h2d_bytes_per_step": B * (784 + 8), "d2h_bytes_per_step": 4,
-                "api": "data.U8BatchLoader -> parallel.MLPTrainEngine.step -> loss.copy_(pinned)"},
+                "api": "data.U8BatchLoader -> parallel.MLPTrainEngine.stage/step -> loss.copy_(pinned)"},
         "gpu_launches": launches_per_step * K,
         "gpu_launches_per_step": launches_per_step,
         "tflops_fp32_equiv": round(flops / (ms / 1e3) / 1e12, 2),
@@ -329,7 +338,7 @@ def main():
     ap.add_argument("--batch-per-gpu", type=int, default=int(os.environ.get("RTDC_BENCH_BATCH", 18944)),
                     help="per-GPU batch; 18944 = 148 SMs x 128 rows, i.e. exactly two waves of 128x256 output tiles")
     ap.add_argument("--rotate", type=int, default=4, help="distinct device-resident input batches for the device-timed loop")
-    ap.add_argument("--lookahead", type=int, default=2, help="H2D batches in flight ahead of the consumer (e2e loop)")
+    ap.add_argument("--lookahead", type=int, default=3, help="H2D batches in flight ahead of the consumer (e2e loop)")
     ap.add_argument("--algo", default="auto", choices=["auto", "two_shot", "nvls"])
     args = ap.parse_args()
     if args.impl == "reference":

@@ -147,6 +147,9 @@ int rtdc_u8_normalize(const uint8_t* src, float* dst, size_t n, float mean, floa
 /* uint8 -> fp32 x*scale + shift (one fma). scale = 1, shift = 0 widens raw pixels exactly, the form the exact-operand
  * GEMM path (rtdc_gemm_desc.a_exact / b_exact) consumes. */
 int rtdc_u8_affine(const uint8_t* src, float* dst, size_t n, float scale, float shift, void* stream);
+/* Same with the grid capped at `blocks` thread blocks (0 = no cap): a conversion that runs on a side stream next to a
+ * tensor-bound kernel is paced down so that it does not fight that kernel for issue slots and L2 bandwidth. */
+int rtdc_u8_affine_paced(const uint8_t* src, float* dst, size_t n, float scale, float shift, int blocks, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Fused optimizer steps over a flat parameter arena (K7). hyper points to device memory so a

@@ -536,6 +536,17 @@ RTDC_API int rtdc_u8_affine(const uint8_t* src, float* dst, size_t n, float scal
   return RTDC_OK;
 }
 
+RTDC_API int rtdc_u8_affine_paced(const uint8_t* src, float* dst, size_t n, float scale, float shift, int blocks, void* stream) {
+  if (!src || !dst) return fail(RTDC_ERR_ARG, "u8_affine: null pointer");
+  if (n == 0) return RTDC_OK;
+  if ((reinterpret_cast<uintptr_t>(src) & 15u) || (reinterpret_cast<uintptr_t>(dst) & 15u)) return fail(RTDC_ERR_ARG, "u8_affine: pointers must be 16-byte aligned");
+  int grid = grid_for(n / 16 + 1, 256, 8);
+  if (blocks > 0 && blocks < grid) grid = blocks;
+  u8_normalize_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(src, dst, n, scale, shift);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
 namespace rtdc {
 // out[n] = bias[n] + t * sum_k w[n, k]: one warp per row, 4 independent float4 loads per lane in flight,
 // fixed summation order (lane-strided partials, then a shuffle tree).

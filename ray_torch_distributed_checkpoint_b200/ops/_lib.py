@@ -76,6 +76,8 @@ def _declare(lib):
     lib.rtdc_colsum.argtypes = [vp, i, i, i, vp, vp, sz, vp]
     lib.rtdc_u8_normalize.argtypes = [vp, vp, sz, f, f, vp]
     lib.rtdc_u8_affine.argtypes = [vp, vp, sz, f, f, vp]
+    lib.rtdc_u8_affine_paced.argtypes = [vp, vp, sz, f, f, i, vp]
+    lib.rtdc_u8_affine_paced.restype = i
     lib.rtdc_fold_input_bias.argtypes = [vp, i, i, i, vp, f, vp, vp]
     lib.rtdc_sgd_step.argtypes = [vp, vp, vp, sz, vp, vp]
     lib.rtdc_adam_step.argtypes = [vp, vp, vp, vp, sz, vp, vp]

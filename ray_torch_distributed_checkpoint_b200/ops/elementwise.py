@@ -100,14 +100,16 @@ def u8_normalize(src: torch.Tensor, *, mean: float = 0.5, std: float = 0.5, out:
 
 
 def u8_affine(src: torch.Tensor, *, scale: float = 1.0, shift: float = 0.0, out: Optional[torch.Tensor] = None,
-              stream=None) -> torch.Tensor:
+              blocks: int = 0, stream=None) -> torch.Tensor:
     """uint8 -> float32 ``x*scale + shift``; the defaults widen raw pixels exactly (every value is then exact in
-    tf32, which is what ``gemm(..., a_exact/b_exact)`` wants)."""
+    tf32, which is what ``gemm(..., a_exact/b_exact)`` wants). ``blocks`` caps the grid (0 = full speed) for a
+    conversion that shares the GPU with a tensor-bound kernel."""
     if src.dtype != torch.uint8 or not src.is_cuda or not src.is_contiguous():
         raise ValueError("src must be a contiguous uint8 CUDA tensor")
     if out is None:
         out = torch.empty(src.shape, dtype=torch.float32, device=src.device)
-    _lib.check(_lib.load().rtdc_u8_affine(src.data_ptr(), out.data_ptr(), src.numel(), scale, shift, _lib.stream_ptr(stream)))
+    _lib.check(_lib.load().rtdc_u8_affine_paced(src.data_ptr(), out.data_ptr(), src.numel(), scale, shift, blocks,
+                                                _lib.stream_ptr(stream)))
     return out
 
 

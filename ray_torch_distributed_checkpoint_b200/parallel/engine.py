@@ -108,9 +108,18 @@ class MLPTrainEngine:
 
         # ---- static activations (graph replays need fixed addresses)
         B = self.B
-        self.x_u8 = torch.zeros(B, self.d_in, dtype=torch.uint8, device=dev)
-        self.x = torch.zeros(B, self.d_in, device=dev)
-        self.y = torch.zeros(B, dtype=torch.int64, device=dev)
+        # two input slots: batch i+1 is staged (copied in and converted) on its own stream while step i runs
+        self.x_u8 = [torch.zeros(B, self.d_in, dtype=torch.uint8, device=dev) for _ in range(2)]
+        self.x = [torch.zeros(B, self.d_in, device=dev) for _ in range(2)]
+        self.y = [torch.zeros(B, dtype=torch.int64, device=dev) for _ in range(2)]
+        self.stage_stream = torch.cuda.Stream(dev)
+        import os as _os
+        self.stage_blocks = int(_os.environ.get("RTDC_STAGE_BLOCKS", "0"))   # optional grid cap of an overlapped conversion (0 = full speed: measured best)
+        self._ready: List[Optional[torch.cuda.Event]] = [None, None]   # slot staged
+        self._free: List[Optional[torch.cuda.Event]] = [None, None]    # last consumer of the slot done
+        self._staged: List[tuple] = []                                  # FIFO of (slot, from_u8)
+        self._next_slot = 0
+        self._stage_done: Optional[torch.cuda.Event] = None
         self.h1 = torch.empty(B, self.d_h, device=dev)
         self.h2 = torch.empty(B, self.d_h, device=dev)
         self.z = torch.zeros(B, _LOGIT_LD, device=dev)
@@ -127,7 +136,7 @@ class MLPTrainEngine:
         self.lr, self.momentum, self.weight_decay = lr, momentum, weight_decay
         self.steps_done = 0
         self.use_graph = use_graph
-        self._graphs: Dict[str, torch.cuda.CUDAGraph] = {}
+        self._graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
         self._warm: Dict[str, int] = {}
         self.stream = torch.cuda.Stream(dev)
         self.kernel_launches_per_step = {}
@@ -160,39 +169,49 @@ class MLPTrainEngine:
                              stream=self.comm_stream)
 
     # ------------------------------------------------------------------------------------------ the step
-    def _forward(self, s, train: bool, from_u8: bool, with_logits: bool = True):
+    def _convert_input(self, src_u8: torch.Tensor, slot: int, s, paced: bool) -> int:
+        """uint8 pixels -> the fp32 operand layer 1 consumes (``self.x[slot]``), on stream ``s``. ``paced``: the
+        conversion overlaps a running step, so its grid is capped (``stage_blocks``) to stay out of the GEMMs' way."""
+        blocks = self.stage_blocks if paced else 0
+        if self.input_mode == "shift":
+            ops.u8_affine(src_u8, shift=self.in_shift / self.in_scale, out=self.x[slot], blocks=blocks, stream=s)   # pixel - 127.5
+        elif self.input_mode == "fold":
+            ops.u8_affine(src_u8, out=self.x[slot], blocks=blocks, stream=s)                                        # raw pixels
+        else:
+            ops.u8_affine(src_u8, scale=self.in_scale, shift=self.in_shift, out=self.x[slot], blocks=blocks, stream=s)
+        return 1
+
+    def _forward(self, s, train: bool, from_u8: bool, slot: int, with_logits: bool = True):
         n = 0
         p = self.p_drop if train else 0.0
         kw = dict(seed=self.seed, step_tensor=self.step_counter, precision=self.precision, stream=s)
+        x = self.x[slot]
         if from_u8 and self.input_mode == "shift":
-            ops.u8_affine(self.x_u8, shift=self.in_shift / self.in_scale, out=self.x, stream=s); n += 1   # pixel - 127.5: exact
-            ops.linear_forward(self.x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, x_exact=True,
+            ops.linear_forward(x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, x_exact=True,
                                alpha=self.in_scale, **kw); n += 1
         elif from_u8 and self.input_mode == "fold":
-            ops.u8_affine(self.x_u8, out=self.x, stream=s); n += 1                       # raw pixels, exact in tf32
             ops.fold_input_bias(self.W[0], self.b[0], self.in_shift, out=self.b1_eff, stream=s); n += 1
-            ops.linear_forward(self.x, self.W[0], self.b1_eff, relu=True, drop_p=p, salt=1, out=self.h1, x_exact=True,
+            ops.linear_forward(x, self.W[0], self.b1_eff, relu=True, drop_p=p, salt=1, out=self.h1, x_exact=True,
                                alpha=self.in_scale, **kw); n += 1
         else:
-            if from_u8:
-                ops.u8_normalize(self.x_u8, mean=self.mean, std=self.std, out=self.x, stream=s); n += 1
-            ops.linear_forward(self.x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, **kw); n += 1
+            ops.linear_forward(x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, **kw); n += 1
         ops.linear_forward(self.h1, self.W[1], self.b[1], relu=True, drop_p=p, salt=2, out=self.h2, **kw); n += 1
         if with_logits:
             ops.linear_forward(self.h2, self.W[2], self.b[2], relu=True, out=self.z, n_store=_LOGIT_LD, **kw); n += 1
         return n
 
-    def _enqueue_train_step(self, s: torch.cuda.Stream, from_u8: bool) -> int:
+    def _enqueue_train_step(self, s: torch.cuda.Stream, from_u8: bool, slot: int) -> int:
         B, prec = self.B, self.precision
         inv_keep = 1.0 / (1.0 - self.p_drop) if self.p_drop > 0 else 1.0
         fused_head = self.fused_head
-        n = self._forward(s, True, from_u8, with_logits=not fused_head)
+        n = self._forward(s, True, from_u8, slot, with_logits=not fused_head)
+        x, y = self.x[slot], self.y[slot]
         if fused_head:
             # layer 3 forward + loss + layer 3 backward in one pass over h2 (exact fp32 on the CUDA cores)
-            ops.mlp_head_train(self.h2, self.W[2], self.b[2], self.y, dh=self.dh2, dw=self.dW[2], db=self.db[2], loss=self.loss,
+            ops.mlp_head_train(self.h2, self.W[2], self.b[2], y, dh=self.dh2, dw=self.dW[2], db=self.db[2], loss=self.loss,
                                grad_scale=1.0 / B, mask_scale=inv_keep, db_below=self.db[1], stream=s); n += 2   # also emits db2
         else:
-            ops.softmax_cross_entropy(self.z, self.y, classes=self.d_out, dlogits=self.dz, grad_scale=1.0 / B, relu_mask=True,
+            ops.softmax_cross_entropy(self.z, y, classes=self.d_out, dlogits=self.dz, grad_scale=1.0 / B, relu_mask=True,
                                       loss_out=self.loss, dbias_out=self.db[2], stream=s); n += 1   # also emits db3
             ops.linear_wgrad(self.dz, self.h2, N_out=self.d_out, out=self.dW[2], precision=prec, stream=s); n += 2
             ops.linear_dgrad(self.dz, self.W[2], N_out=self.d_out, mask_src=self.h2, mask_scale=inv_keep, out=self.dh2,
@@ -210,12 +229,12 @@ class MLPTrainEngine:
         # layer 1 (its input needs no gradient); with folded input dW1 = s*(dh1^T raw) + t*db1 1^T
         ops.colsum(self.dh1_colsum, out=self.db[0], stream=s); n += 1
         if from_u8 and self.input_mode == "shift":
-            ops.linear_wgrad(self.dh1, self.x, out=self.dW[0], precision=prec, x_exact=True, alpha=self.in_scale, stream=s); n += 2
+            ops.linear_wgrad(self.dh1, x, out=self.dW[0], precision=prec, x_exact=True, alpha=self.in_scale, stream=s); n += 2
         elif from_u8 and self.input_mode == "fold":
-            ops.linear_wgrad(self.dh1, self.x, out=self.dW[0], precision=prec, x_exact=True, alpha=self.in_scale,
+            ops.linear_wgrad(self.dh1, x, out=self.dW[0], precision=prec, x_exact=True, alpha=self.in_scale,
                              row_bias=self.db[0], row_bias_scale=self.in_shift, stream=s); n += 2
         else:
-            ops.linear_wgrad(self.dh1, self.x, out=self.dW[0], precision=prec, stream=s); n += 2
+            ops.linear_wgrad(self.dh1, x, out=self.dW[0], precision=prec, stream=s); n += 2
         for b in range(len(self.buckets)):
             if b not in launched:
                 self._reduce_bucket(b, s); n += self.world > 1
@@ -225,58 +244,99 @@ class MLPTrainEngine:
         ops.counter_advance(self.step_counter, self.sgd, stream=s); n += 1
         return n
 
-    def _enqueue_eval(self, s: torch.cuda.Stream, from_u8: bool) -> int:
-        n = self._forward(s, False, from_u8)
-        ops.softmax_cross_entropy(self.z, self.y, classes=self.d_out, loss_out=self.loss, loss_sum_accum=self.eval_loss_sum,
+    def _enqueue_eval(self, s: torch.cuda.Stream, from_u8: bool, slot: int) -> int:
+        n = self._forward(s, False, from_u8, slot)
+        ops.softmax_cross_entropy(self.z, self.y[slot], classes=self.d_out, loss_out=self.loss, loss_sum_accum=self.eval_loss_sum,
                                   correct_accum=self.eval_correct, stream=s)
         return n + 1
 
-    def _run(self, key: str, enqueue):
-        """Two eager warm-up executions (allocations, scratch, first-step flag), then capture + replay."""
+    def _run(self, key: str, slot: int, enqueue):
+        """Two eager warm-up executions (allocations, scratch, first-step flag), then capture (both input slots at
+        once, so no capture falls into a later step) + replay."""
         s = self.stream
-        s.wait_stream(torch.cuda.current_stream(self.device))
+        cur = torch.cuda.current_stream(self.device)
+        s.wait_stream(cur)
+        if self._ready[slot] is not None:
+            s.wait_event(self._ready[slot])
         with torch.cuda.stream(s):
             if not self.use_graph or self._warm.get(key, 0) < 2:
-                self.kernel_launches_per_step[key] = enqueue(s)
+                self.kernel_launches_per_step[key] = enqueue(s, slot) + (1 if key.endswith("u8") else 0)   # + the staging kernel
                 self._warm[key] = self._warm.get(key, 0) + 1
             else:
-                g = self._graphs.get(key)
-                if g is None:
+                if (key, slot) not in self._graphs:
                     if self.world > 1:
                         dist.barrier(group=self.group)      # all ranks capture (and first replay) together
-                    g = torch.cuda.CUDAGraph()
-                    with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
-                        self.kernel_launches_per_step[key] = enqueue(s)
-                    self._graphs[key] = g
-                g.replay()
-        torch.cuda.current_stream(self.device).wait_stream(s)
-
-    def _load_inputs(self, x: torch.Tensor, y: torch.Tensor) -> bool:
-        """Copy a batch into the static input buffers (H2D when ``x``/``y`` live in pinned host memory,
-        D2D otherwise). Returns True when ``x`` is uint8 pixels that still need normalising."""
-        if x.shape[0] != self.B:
-            raise ValueError(f"engine was built for batches of {self.B} samples (got {x.shape[0]})")
-        x2 = x.reshape(self.B, -1)
-        self.y.copy_(y, non_blocking=True)
-        if x2.dtype == torch.uint8:
-            self.x_u8.copy_(x2, non_blocking=True)
-            return True
-        self.x.copy_(x2, non_blocking=True)
-        return False
+                    for sl in (0, 1):
+                        g = torch.cuda.CUDAGraph()
+                        with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
+                            enqueue(s, sl)
+                        self._graphs[(key, sl)] = g
+                self._graphs[(key, slot)].replay()
+            ev = torch.cuda.Event()
+            ev.record(s)
+            self._free[slot] = ev
+        cur.wait_stream(s)
+        if self._stage_done is not None:
+            cur.wait_event(self._stage_done)     # orders the caller's stream after the staging reads of its tensors
 
     # ------------------------------------------------------------------------------------------ public API
-    def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
-        """One optimizer step on a batch (uint8 pixels or normalised float32). Returns the device-resident
-        mean loss of this rank's batch (``.item()`` to read it back)."""
-        from_u8 = self._load_inputs(x, y)
-        self._run("train_u8" if from_u8 else "train_f32", lambda s: self._enqueue_train_step(s, from_u8))
+    def stage(self, x: torch.Tensor, y: torch.Tensor, _paced: bool = True) -> None:
+        """Copy a batch in (H2D from pinned host memory, or straight from a device tensor) and convert it for layer 1
+        on the staging stream. Call it for batch i+1 *before* ``step()`` of batch i: the copy and the uint8 -> fp32
+        conversion then run concurrently with that step instead of in front of the next one. At most two batches can
+        be staged."""
+        if x.shape[0] != self.B:
+            raise ValueError(f"engine was built for batches of {self.B} samples (got {x.shape[0]})")
+        if len(self._staged) >= 2:
+            raise RuntimeError("two batches are already staged; call step() first")
+        slot = self._next_slot
+        self._next_slot ^= 1
+        st = self.stage_stream
+        st.wait_stream(torch.cuda.current_stream(self.device))     # x / y were produced on the caller's stream
+        if self._free[slot] is not None:
+            st.wait_event(self._free[slot])                          # the step that last read this slot is done
+        from_u8 = x.dtype == torch.uint8
+        with torch.cuda.stream(st):
+            for t in (x, y):
+                if t.is_cuda:
+                    t.record_stream(st)                              # the caller may drop its reference right away
+            x2 = x.reshape(self.B, -1)
+            self.y[slot].copy_(y, non_blocking=True)
+            if from_u8:
+                if x2.is_cuda and x2.is_contiguous() and x2.data_ptr() % 16 == 0:
+                    src = x2                                         # convert straight out of the caller's buffer
+                else:
+                    self.x_u8[slot].copy_(x2, non_blocking=True)
+                    src = self.x_u8[slot]
+                self._convert_input(src, slot, st, paced=_paced)
+            else:
+                self.x[slot].copy_(x2, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(st)
+        self._ready[slot] = ev
+        self._stage_done = ev
+        self._staged.append((slot, from_u8))
+
+    def _consume(self, x, y):
+        if x is not None:
+            self.stage(x, y, _paced=False)       # nothing to overlap with: convert at full speed
+        if not self._staged:
+            raise RuntimeError("no staged batch: call stage(x, y) first or pass the batch to step()")
+        return self._staged.pop(0)
+
+    def step(self, x: Optional[torch.Tensor] = None, y: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """One optimizer step on a batch (uint8 pixels or normalised float32): either the batch passed in, or the
+        oldest one handed to :meth:`stage`. Returns the device-resident mean loss of this rank's batch
+        (``.item()`` to read it back)."""
+        slot, from_u8 = self._consume(x, y)
+        self._run("train_u8" if from_u8 else "train_f32", slot, lambda s, sl: self._enqueue_train_step(s, from_u8, sl))
         self.steps_done += 1
         return self.loss
 
-    def eval_batch(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+    def eval_batch(self, x: Optional[torch.Tensor] = None, y: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Forward + loss on a batch, accumulating ``eval_loss_sum`` / ``eval_correct`` on the device."""
-        from_u8 = self._load_inputs(x, y)
-        self._run("eval_u8" if from_u8 else "eval_f32", lambda s: self._enqueue_eval(s, from_u8))
+        slot, from_u8 = self._consume(x, y)
+        self._run("eval_u8" if from_u8 else "eval_f32", slot, lambda s, sl: self._enqueue_eval(s, from_u8, sl))
         return self.loss
 
     def reset_eval(self):
@@ -289,9 +349,11 @@ class MLPTrainEngine:
 
     def predict(self, x: torch.Tensor) -> torch.Tensor:
         """Logits ``[B, classes]`` for a batch (eval mode)."""
-        from_u8 = self._load_inputs(x, torch.zeros(self.B, dtype=torch.int64, device=self.device))
+        slot, from_u8 = self._consume(x, torch.zeros(self.B, dtype=torch.int64, device=self.device))
         s = torch.cuda.current_stream(self.device)
-        self._forward(s, False, from_u8)
+        s.wait_event(self._ready[slot])
+        self._forward(s, False, from_u8, slot)
+        ev = torch.cuda.Event(); ev.record(s); self._free[slot] = ev
         return self.z[:, :self.d_out].clone()
 
     def set_lr(self, lr: float):

@@ -61,7 +61,7 @@ def test_engine_matches_reference_training(use_graph, fused_head):
         # one ReLU unit flipping between fp32 and fp64 moves a gradient row by ~1/B of its norm
         assert diff.norm() / ref.norm() < 2e-2, (i, float(diff.norm() / ref.norm()))
     if use_graph:
-        assert "train_f32" in eng._graphs
+        assert ("train_f32", 0) in eng._graphs and ("train_f32", 1) in eng._graphs
     assert eng.kernel_launches_per_step["train_f32"] >= 12
     eng.close()
 
@@ -120,5 +120,22 @@ def test_engine_eval_u8_and_state_roundtrip():
     assert list(fresh.state_dict()) == list(e2.model_state_dict(prefix=""))
     e3.load_optimizer_state_dict(e2.optimizer_state_dict())
     assert torch.equal(e3.m_arena, e2.m_arena)
-    for e in (eng, e2, e3, e4, e5, e6):
+    # staged (pipelined) use gives the same training trajectory as passing each batch to step()
+    kw = dict(batch_size=B, device="cuda", distributed=False, seed=11)
+    ea, eb = MLPTrainEngine(NeuralNetwork(), **kw), MLPTrainEngine(NeuralNetwork(), **kw)
+    eb.load_model_state_dict(ea.model_state_dict())
+    batches = [(torch.randint(0, 256, (B, 28, 28), dtype=torch.uint8, device="cuda"), torch.randint(0, 10, (B,), device="cuda"))
+               for _ in range(6)]
+    la = [ea.step(xb, yb).item() for xb, yb in batches]
+    lb = []
+    eb.stage(*batches[0])
+    for i in range(len(batches)):
+        if i + 1 < len(batches):
+            eb.stage(*batches[i + 1])          # next batch's conversion overlaps this step
+        lb.append(eb.step().item())
+    assert la == lb
+    assert torch.equal(ea.p_arena, eb.p_arena)
+    with pytest.raises(RuntimeError):
+        eb.step()
+    for e in (eng, e2, e3, e4, e5, e6, ea, eb):
         e.close()
