@@ -210,3 +210,25 @@ def test_multi_tile_n_not_multiple_of_32(bn):
     ops.gemm(a, b, out, bn=bn, splits=1)
     ref = a.double() @ b.double().T
     assert (out.double() - ref).abs().max().item() < 4e-6 * (a.double().abs() @ b.double().abs().T).max().item()
+
+
+@pytest.mark.parametrize("M,N", [(300, 512), (384, 160), (129, 130), (640, 784)])
+def test_output_stays_inside_its_rows(M, N):
+    """Canary rows behind the output (and behind the split-K result) stay untouched: the CTA-pair kernel schedules a
+    phantom half-tile past M when the number of 128-row tiles is odd, TMA stores clip at the tensor edge."""
+    ops = _ops()
+    torch.manual_seed(9)
+    K = 96
+    a, b = torch.randn(M, K, device="cuda"), torch.randn(N, K, device="cuda")
+    ld = (N + 3) // 4 * 4
+    arena = torch.full((M + 130, ld), 5.0, device="cuda")
+    ops.gemm(a, b, arena[:M], N=N, splits=1)
+    ref = a.double() @ b.double().T
+    assert (arena[:M, :N].double() - ref).abs().max().item() < 4e-6 * (a.double().abs() @ b.double().abs().T).max().item()
+    assert bool((arena[M:] == 5.0).all())
+    # split-K twin (wgrad shape)
+    dy, x = torch.randn(2048, (M + 3) // 4 * 4, device="cuda"), torch.randn(2048, ld, device="cuda")
+    arena.fill_(5.0)
+    ops.linear_wgrad(dy, x, N_out=M, out=arena[:M])
+    assert bool((arena[M:] == 5.0).all())
+    assert (arena[:M].double() - dy[:, :M].double().T @ x.double()).abs().max().item() < 1e-3
