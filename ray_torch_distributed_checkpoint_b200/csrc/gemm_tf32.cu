@@ -43,6 +43,9 @@ struct GemmParams {
   int bn, stages, splits, kb_per_split, num_kb;
   int m_tiles, n_tiles;
   int m_tiles2;   // 256-row tiles (CTA-pair kernel)
+  // weighted split-K: the tiles of the last (narrower) N column get their own split count, so that every work unit costs
+  // about the same. Units are numbered: [tiles_full x splits] first, then [m_sched x splits_last].
+  int m_sched, tiles_full, full_units, total_units, splits_last, kb_per_split_last;
   uint32_t a_bytes, b_bytes, stage_bytes;  // per stage: raw A, raw B, total (incl. tails when split)
   float* out; int ldo; int n_store;
   const float* bias; int relu;
@@ -56,9 +59,29 @@ struct GemmParams {
   uint32_t a_tail_off, b_tail_off;        // tail tiles, bytes from the start of a stage
   uint32_t split_lo_vec, split_hi_vec;    // float4 range of the raw tiles the splitters have to process
   float alpha; const float* row_bias; float row_bias_scale;
+  // MN-major operands: tiles that lie inside the first a3_limit / b3_limit rows (whole 32-element blocks) are loaded by
+  // ONE 3-D TMA instruction ([blocks][k][32]) instead of one 2-D box per 32 rows; 0 = no 3-D map
+  int a3_limit, b3_limit;
   int tma_store;         // epilogue goes through smem + cp.async.bulk.tensor stores (tmOut valid)
   long long* dbg_times;  // RTDC_GEMM_DEBUG_BUF: per-CTA clock64 stamps [grid][8]
 };
+
+struct Unit { int tile, split, kb_begin, n_iters; };
+// Work unit -> (tile, K split, K-block range). Tiles are numbered n_tile * m_sched + m_idx, so the last N column's tiles
+// are the last m_sched ones.
+__device__ __forceinline__ Unit decode_unit(const GemmParams& p, int u) {
+  Unit w;
+  int kps;
+  if (u < p.full_units) {
+    w.tile = u % p.tiles_full; w.split = u / p.tiles_full; kps = p.kb_per_split;
+  } else {
+    const int v = u - p.full_units;
+    w.tile = p.tiles_full + v % p.m_sched; w.split = v / p.m_sched; kps = p.kb_per_split_last;
+  }
+  w.kb_begin = w.split * kps;
+  w.n_iters = min(p.num_kb, w.kb_begin + kps) - w.kb_begin;
+  return w;
+}
 
 // keep flag for dropout: 16 random bits per element, 8 elements per Philox call.
 __device__ __forceinline__ uint32_t rand16(const Philox4& r, int j) {
@@ -256,7 +279,8 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
 template <bool A_MN, bool B_MN, int NSPLIT, int BK>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmOut, const GemmParams p) {
+                 const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmA3,
+                 const __grid_constant__ CUtensorMap tmB3, const GemmParams p) {
   extern __shared__ uint8_t smem_dyn[];
   __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t ready_bar[MAX_STAGES];
@@ -291,6 +315,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     if (p.tma_store) tma_prefetch_desc(&tmOut);
+    if (p.a3_limit) tma_prefetch_desc(&tmA3);
+    if (p.b3_limit) tma_prefetch_desc(&tmB3);
   }
   if (warp == 1) {
     tmem_alloc(&tmem_base_slot, TMEM_COLS);
@@ -306,8 +332,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // A CTA walks over work units (output tile x K split) round-robin; every role derives the same
   // sequence, so the smem ring and the two TMEM accumulator buffers just keep cycling across units and
   // the epilogue of unit j overlaps the main loop of unit j+1.
-  const int tiles = p.m_tiles * p.n_tiles;
-  const int total_units = tiles * p.splits;
+  const int total_units = p.total_units;
   // the splitter warps help with the CTA's final epilogue when the ring can host their four store boxes
   const bool share_final = !(p.debug & 32) && static_cast<uint32_t>(p.stages) * p.stage_bytes >= 32768u;
 
@@ -317,10 +342,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int s = 0;
       uint32_t ph = 0;
       for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-        const int tile = u % tiles, split = u / tiles;
+        const Unit w = decode_unit(p, u);
+        const int tile = w.tile, kb_begin = w.kb_begin, n_iters = w.n_iters;
         const int m0 = (tile % p.m_tiles) * BM, n0 = (tile / p.m_tiles) * p.bn;
-        const int kb_begin = split * p.kb_per_split;
-        const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
         for (int it = 0; it < n_iters; ++it) {
           mbar_wait(&empty_bar[s], ph ^ 1u);
           uint8_t* sa = ring_ptr + static_cast<size_t>(s) * p.stage_bytes;
@@ -332,12 +356,16 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int k0 = (kb_begin + it) * BK;
             if (!A_MN) {
               tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
+            } else if (m0 + BM <= p.a3_limit) {
+              tma_load_3d(sa, &tmA3, &full_bar[s], 0, k0, m0 >> 5);
             } else {
 #pragma unroll
               for (int b = 0; b < BM / 32; ++b) tma_load_2d(sa + b * (128 * BK), &tmA, &full_bar[s], m0 + 32 * b, k0);
             }
             if (!B_MN) {
               tma_load_2d(sb, &tmB, &full_bar[s], k0, n0);
+            } else if (n0 + p.bn <= p.b3_limit) {
+              tma_load_3d(sb, &tmB3, &full_bar[s], 0, k0, n0 >> 5);
             } else {
               for (int b = 0; b < p.bn / 32; ++b) tma_load_2d(sb + b * (128 * BK), &tmB, &full_bar[s], n0 + 32 * b, k0);
             }
@@ -366,10 +394,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t ph = 0;
       int j = 0;
       for (int u = blockIdx.x; u < total_units; u += gridDim.x, ++j) {
-        const int tile = u % tiles, split = u / tiles;
+        const Unit w = decode_unit(p, u);
+        const int tile = w.tile, kb_begin = w.kb_begin, n_iters = w.n_iters;
         const int n0 = (tile / p.m_tiles) * p.bn;
-        const int kb_begin = split * p.kb_per_split;
-        const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
         const int n_valid = min(p.bn, p.N - n0);
         const uint32_t umma_n = static_cast<uint32_t>(min(p.bn, (n_valid + 15) & ~15));
         const uint32_t idesc = umma_idesc(UMMA_TF32, A_MN, B_MN, umma_n);
@@ -429,9 +456,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int s = 0;
       uint32_t ph = 0;
       for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-        const int split = u / tiles;
-        const int kb_begin = split * p.kb_per_split;
-        const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
+        const int n_iters = decode_unit(p, u).n_iters;
         for (int it = 0; it < n_iters; ++it) {
           mbar_wait(&full_bar[s], ph);
           const float4* raw = reinterpret_cast<const float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes);
@@ -470,7 +495,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (share_final) {
       const int n_mine = (total_units - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
       const int j = n_mine - 1, u = static_cast<int>(blockIdx.x) + j * static_cast<int>(gridDim.x);
-      const int tile = u % tiles, split = u / tiles;
+      const Unit w = decode_unit(p, u);
+      const int tile = w.tile, split = w.split;
       const int m0 = (tile % p.m_tiles) * BM, n0 = (tile / p.m_tiles) * p.bn;
       const int n_valid = min(p.bn, p.N - n0);
       const int umma_n = min(p.bn, (n_valid + 15) & ~15);
@@ -498,7 +524,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint32_t stores_issued = 0;
     int j = 0;
     for (int u = blockIdx.x; u < total_units; u += gridDim.x, ++j) {
-      const int tile = u % tiles, split = u / tiles;
+      const Unit w = decode_unit(p, u);
+      const int tile = w.tile, split = w.split;
       const int m0 = (tile % p.m_tiles) * BM, n0 = (tile / p.m_tiles) * p.bn;
       const int n_valid = min(p.bn, p.N - n0);
       const int umma_n = min(p.bn, (n_valid + 15) & ~15);
@@ -542,7 +569,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 template <bool A_MN, bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                        const __grid_constant__ CUtensorMap tmOut, const GemmParams p) {
+                        const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmA3,
+                        const __grid_constant__ CUtensorMap tmB3, const GemmParams p) {
   constexpr int BK = 16;
   extern __shared__ uint8_t smem_dyn[];
   __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
@@ -580,6 +608,8 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     if (p.tma_store) tma_prefetch_desc(&tmOut);
+    if (p.a3_limit) tma_prefetch_desc(&tmA3);
+    if (p.b3_limit) tma_prefetch_desc(&tmB3);
   }
   if (warp == 1) {
     tmem_alloc_2cta(&tmem_base_slot, TMEM_COLS);
@@ -591,8 +621,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
   tcgen05_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
-  const int tiles2 = p.m_tiles2 * p.n_tiles;
-  const int total_units = tiles2 * p.splits;
+  const int total_units = p.total_units;
   const int half_bn = p.bn >> 1;
   // RTDC_GEMM_DEBUG_BUF: per-CTA stamps [grid][16]: 0 start clk, 1/2 first-unit epilogue begin/end, 3/4 last-unit epilogue
   // begin/end, 5 end clk, 6/7 end/start ns, 8/9 issuer: first/last unit's MMAs issued
@@ -606,14 +635,13 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       int s = 0;
       uint32_t ph = 0;
       for (int u = pair; u < total_units; u += num_pairs) {
-        const int tile2 = u % tiles2, split = u / tiles2;
+        const Unit w = decode_unit(p, u);
+        const int tile2 = w.tile, kb_begin = w.kb_begin, n_iters = w.n_iters;
         const int m0 = (tile2 % p.m_tiles2) * (2 * BM) + static_cast<int>(rank) * BM;
         const int n0 = (tile2 / p.m_tiles2) * p.bn;
         const int gran2 = B_MN ? 64 : 32;
         const int umma_n = min(p.bn, (min(p.bn, p.N - n0) + gran2 - 1) / gran2 * gran2);   // this tile's MMA width
         const int nb0 = n0 + static_cast<int>(rank) * (umma_n >> 1);                          // this CTA's half of it
-        const int kb_begin = split * p.kb_per_split;
-        const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
         for (int it = 0; it < n_iters; ++it) {
           mbar_wait(&empty_bar[s], ph ^ 1u);
           uint8_t* sa = ring_ptr + static_cast<size_t>(s) * p.stage_bytes;
@@ -623,12 +651,16 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
           const int k0 = (kb_begin + it) * BK;
           if (!A_MN) {
             tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
+          } else if (m0 + BM <= p.a3_limit) {
+            tma_load_3d(sa, &tmA3, &full_bar[s], 0, k0, m0 >> 5);
           } else {
 #pragma unroll
             for (int b = 0; b < BM / 32; ++b) tma_load_2d(sa + b * (128 * BK), &tmA, &full_bar[s], m0 + 32 * b, k0);
           }
           if (!B_MN) {
             tma_load_2d(sb, &tmB, &full_bar[s], k0, nb0);
+          } else if (nb0 + half_bn <= p.b3_limit) {
+            tma_load_3d(sb, &tmB3, &full_bar[s], 0, k0, nb0 >> 5);
           } else {
             for (int b = 0; b < half_bn / 32; ++b) tma_load_2d(sb + b * (128 * BK), &tmB, &full_bar[s], nb0 + 32 * b, k0);
           }
@@ -652,9 +684,8 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       uint32_t ph = 0;
       int j = 0;
       for (int u = pair; u < total_units; u += num_pairs, ++j) {
-        const int tile2 = u % tiles2, split = u / tiles2;
-        const int kb_begin = split * p.kb_per_split;
-        const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
+        const Unit w = decode_unit(p, u);
+        const int tile2 = w.tile, kb_begin = w.kb_begin, n_iters = w.n_iters;
         const int n0 = (tile2 / p.m_tiles2) * p.bn;
         const int gran2 = B_MN ? 64 : 32;
         const int umma_n = min(p.bn, (min(p.bn, p.N - n0) + gran2 - 1) / gran2 * gran2);
@@ -702,9 +733,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
     int s = 0;
     uint32_t ph = 0;
     for (int u = pair; u < total_units; u += num_pairs) {
-      const int split = u / tiles2;
-      const int kb_begin = split * p.kb_per_split;
-      const int n_iters = min(p.num_kb, kb_begin + p.kb_per_split) - kb_begin;
+      const int n_iters = decode_unit(p, u).n_iters;
       for (int it = 0; it < n_iters; ++it) {
         mbar_wait(&full_bar[s], ph);
         const float4* raw = reinterpret_cast<const float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes);
@@ -740,7 +769,8 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
     if (share_final) {
       const int n_mine = (total_units - pair + num_pairs - 1) / num_pairs;
       const int j = n_mine - 1, u = pair + j * num_pairs;
-      const int tile2 = u % tiles2, split = u / tiles2;
+      const Unit w = decode_unit(p, u);
+      const int tile2 = w.tile, split = w.split;
       const int m_tile128 = (tile2 % p.m_tiles2) * 2 + static_cast<int>(rank);
       const int n_tile = tile2 / p.m_tiles2;
       const int m0 = m_tile128 * BM, n0 = n_tile * p.bn;
@@ -771,7 +801,8 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
     uint32_t stores_issued = 0;
     int j = 0;
     for (int u = pair; u < total_units; u += num_pairs, ++j) {
-      const int tile2 = u % tiles2, split = u / tiles2;
+      const Unit w = decode_unit(p, u);
+      const int tile2 = w.tile, split = w.split;
       const int m_tile128 = (tile2 % p.m_tiles2) * 2 + static_cast<int>(rank);
       const int n_tile = tile2 / p.m_tiles2;
       const int m0 = m_tile128 * BM, n0 = n_tile * p.bn;
@@ -807,18 +838,19 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
 // output with bias / ReLU applied. One block = 32 rows x 32 columns of one tile chunk; thread =
 // one float4, so both the scratch reads and the output writes are full 128-byte lines.
 __global__ void __launch_bounds__(256)
-splitk_reduce_kernel(const float* __restrict__ scratch, int splits, int m_tiles, int bn, int M, int N, int n_store,
-                     float* __restrict__ out, int ldo, const float* __restrict__ bias, int relu, float alpha,
+splitk_reduce_kernel(const float* __restrict__ scratch, int splits_full, int splits_last, int n_tiles, int m_tiles, int bn, int M, int N,
+                     int n_store, float* __restrict__ out, int ldo, const float* __restrict__ bias, int relu, float alpha,
                      const float* __restrict__ row_bias, float row_bias_scale) {
   const int chunks = (bn + 31) / 32;
   const int tile = blockIdx.x / chunks, c = blockIdx.x % chunks;
   const int m_tile = tile % m_tiles, n_tile = tile / m_tiles;
+  const int splits = n_tile == n_tiles - 1 ? splits_last : splits_full;   // partial slots are laid out with stride splits_full
   const int r = blockIdx.y * 32 + (threadIdx.x >> 3), q = threadIdx.x & 7;
   const int row = m_tile * BM + r;
   const int col = n_tile * bn + c * 32 + q * 4;
   if (row >= M || col >= n_store || c * 32 + q * 4 >= bn) return;
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-  const float* src = scratch + (static_cast<size_t>(tile) * splits) * (BM * MAX_BN) + (static_cast<size_t>(c) * BM + r) * 32 + q * 4;
+  const float* src = scratch + (static_cast<size_t>(tile) * splits_full) * (BM * MAX_BN) + (static_cast<size_t>(c) * BM + r) * 32 + q * 4;
   if (col < N) {
     constexpr int ZI = 8;   // loads in flight; the sum is still formed in split order
     for (int z0 = 0; z0 < splits; z0 += ZI) {
@@ -889,11 +921,29 @@ static int make_map(CUtensorMap* map, const float* base, int inner, int outer, i
   return RTDC_OK;
 }
 
+// 3-D view of a row-major [k_extent, ld] fp32 matrix whose first `blocks * 32` columns are whole 32-element blocks:
+// (32 contiguous floats, k rows of pitch ld, blocks of pitch 128 B). One box = [box_blocks][box_k][32], which is exactly the
+// shared-memory layout of box_blocks consecutive 2-D MN-major boxes.
+static int make_map3_mn(CUtensorMap* map, const float* base, int blocks, int k_extent, int ld, int box_k, int box_blocks) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return fail(RTDC_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[3] = {32, static_cast<cuuint64_t>(k_extent), static_cast<cuuint64_t>(blocks)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(ld) * 4, 128};
+  cuuint32_t box[3] = {32, static_cast<cuuint32_t>(box_k), static_cast<cuuint32_t>(box_blocks)};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(RTDC_ERR_CUDA, "cuTensorMapEncodeTiled (3-D MN-major view) failed with CUresult %d", static_cast<int>(r));
+  return RTDC_OK;
+}
+
 struct Plan {
   int two_cta, m_tiles2;
   int a_exact, b_exact;
   int bk;
   int bn, stages, splits, kb_per_split, num_kb, m_tiles, n_tiles;
+  int splits_last, kb_per_split_last;   // split count of the last (narrower) N column's tiles, see GemmParams
   uint32_t a_bytes, b_bytes, stage_bytes;
   size_t smem;
 };
@@ -973,6 +1023,37 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
   if (splits > pl->num_kb) splits = pl->num_kb;
   pl->kb_per_split = ceil_div(pl->num_kb, splits);
   pl->splits = ceil_div(pl->num_kb, pl->kb_per_split);  // no empty split
+  pl->splits_last = pl->splits; pl->kb_per_split_last = pl->kb_per_split;
+  // Weighted split-K: when the last N column is narrower than the others its units are cheaper, so it gets fewer splits and
+  // the freed CTAs shorten everybody else's K range. Cost of a unit ~ K blocks x (fixed per-stage work + MMA width).
+  if (d->splits == 0 && pl->splits > 1 && pl->n_tiles > 1) {
+    const int w_last = round_up(d->N - (pl->n_tiles - 1) * bn, gran) < bn ? round_up(d->N - (pl->n_tiles - 1) * bn, gran) : bn;
+    const int m_sched = two_cta ? pl->m_tiles2 : pl->m_tiles;
+    const int sms = (need_device ? num_sms() : 148) / (two_cta ? 2 : 1);
+    const int slots = sms / m_sched, nt = pl->n_tiles;
+    int cap = d->K / 256 < 64 ? d->K / 256 : 64;
+    if (cap < 1) cap = 1;
+    const char* envl = getenv("RTDC_GEMM_SPLITS_LAST");
+    if (w_last < bn && slots >= nt) {
+      const double c_full = 1.0, c_last = 0.75 + 0.25 * static_cast<double>(w_last) / bn;   // measured: a 64-wide unit costs ~80 % of a 256-wide one per K block
+      double best = 1e30;
+      int best_f = pl->splits, best_l = pl->splits;
+      for (int sl = 1; sl <= cap && sl <= slots - (nt - 1); ++sl) {
+        int sf = (slots - sl) / (nt - 1);
+        if (sf > cap) sf = cap;
+        if (sf < sl) continue;                       // partial slots are laid out with stride splits_full
+        if (envl && atoi(envl) != sl) continue;
+        const double cost_f = ceil_div(pl->num_kb, sf) * c_full, cost_l = ceil_div(pl->num_kb, sl) * c_last;
+        const double cost = cost_f > cost_l ? cost_f : cost_l;
+        if (cost <= best + 1e-9) { best = cost; best_f = sf; best_l = sl; }   // ties: more splits for the last column
+      }
+      pl->kb_per_split = ceil_div(pl->num_kb, best_f);
+      pl->splits = ceil_div(pl->num_kb, pl->kb_per_split);
+      pl->kb_per_split_last = ceil_div(pl->num_kb, best_l);
+      pl->splits_last = ceil_div(pl->num_kb, pl->kb_per_split_last);
+      if (pl->splits_last > pl->splits) { pl->splits_last = pl->splits; pl->kb_per_split_last = pl->kb_per_split; }
+    }
+  }
   return RTDC_OK;
 }
 
@@ -984,23 +1065,25 @@ static size_t scratch_bytes_for(const Plan& pl) {
 }
 
 template <bool A_MN, bool B_MN>
-static int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const GemmParams& gp, const Plan& pl, cudaStream_t st) {
+static int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& ta3, const CUtensorMap& tb3,
+                       const GemmParams& gp, const Plan& pl, cudaStream_t st) {
   auto kern = gemm_tf32x3_2cta_kernel<A_MN, B_MN>;
   RTDC_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT - STATIC_SMEM_RESERVE));
-  const int units = pl.m_tiles2 * pl.n_tiles * pl.splits;
+  const int units = gp.total_units;
   const int pairs = units < num_sms() / 2 ? units : num_sms() / 2;   // persistent: one CTA pair per TPC
-  kern<<<2 * pairs, NUM_THREADS, pl.smem, st>>>(ta, tb, to, gp);
+  kern<<<2 * pairs, NUM_THREADS, pl.smem, st>>>(ta, tb, to, ta3, tb3, gp);
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;
 }
 
 template <bool A_MN, bool B_MN, int NSPLIT, int BK>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const GemmParams& gp, const Plan& pl, cudaStream_t st) {
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& ta3, const CUtensorMap& tb3,
+                  const GemmParams& gp, const Plan& pl, cudaStream_t st) {
   auto kern = gemm_tf32_kernel<A_MN, B_MN, NSPLIT, BK>;
   RTDC_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT - STATIC_SMEM_RESERVE));
-  const int units = pl.m_tiles * pl.n_tiles * pl.splits;
+  const int units = gp.total_units;
   const int grid = units < num_sms() ? units : num_sms();   // persistent: one CTA per SM walks the work units
-  kern<<<grid, NUM_THREADS, pl.smem, st>>>(ta, tb, to, gp);
+  kern<<<grid, NUM_THREADS, pl.smem, st>>>(ta, tb, to, ta3, tb3, gp);
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;
 }
@@ -1025,7 +1108,7 @@ RTDC_API int rtdc_gemm_plan(const rtdc_gemm_desc* d, int* out5) {
 }
 
 static int dispatch(const rtdc_gemm_desc* d, bool three, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
-                    const rtdc::GemmParams& gp, const rtdc::Plan& pl, cudaStream_t st);
+                    const CUtensorMap& ta3, const CUtensorMap& tb3, const rtdc::GemmParams& gp, const rtdc::Plan& pl, cudaStream_t st);
 
 RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   Plan pl;
@@ -1048,9 +1131,35 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
 
   GemmParams gp;
   memset(&gp, 0, sizeof(gp));
+  // one-instruction loads of MN-major tiles over the whole 32-element blocks of the operand (RTDC_GEMM_NO_TMA3D=1: off)
+  CUtensorMap ta3, tb3;
+  memset(&ta3, 0, sizeof(ta3)); memset(&tb3, 0, sizeof(tb3));
+  const bool use3 = !getenv("RTDC_GEMM_NO_TMA3D");
+  if (use3 && d->a_mn && d->M >= BM) {
+    rc = make_map3_mn(&ta3, d->a, d->M / 32, d->K, d->lda, pl.bk, BM / 32);
+    if (rc != RTDC_OK) return rc;
+    gp.a3_limit = (d->M / 32) * 32;
+  }
+  const int b_cols = pl.two_cta ? pl.bn / 2 : pl.bn;   // columns of B one CTA stages
+  if (use3 && d->b_mn && d->N >= b_cols) {
+    rc = make_map3_mn(&tb3, d->b, d->N / 32, d->K, d->ldb, pl.bk, b_cols / 32);
+    if (rc != RTDC_OK) return rc;
+    gp.b3_limit = (d->N / 32) * 32;
+  }
   gp.M = d->M; gp.N = d->N; gp.K = d->K;
   gp.bn = pl.bn; gp.stages = pl.stages; gp.splits = pl.splits; gp.kb_per_split = pl.kb_per_split; gp.num_kb = pl.num_kb;
   gp.m_tiles = pl.m_tiles; gp.n_tiles = pl.n_tiles; gp.m_tiles2 = pl.m_tiles2;
+  gp.m_sched = pl.two_cta ? pl.m_tiles2 : pl.m_tiles;
+  gp.splits_last = pl.splits_last; gp.kb_per_split_last = pl.kb_per_split_last;
+  if (pl.splits_last != pl.splits) {
+    gp.tiles_full = gp.m_sched * (pl.n_tiles - 1);
+    gp.full_units = gp.tiles_full * pl.splits;
+    gp.total_units = gp.full_units + gp.m_sched * pl.splits_last;
+  } else {   // uniform: one numbering over all tiles
+    gp.tiles_full = gp.m_sched * pl.n_tiles;
+    gp.full_units = gp.tiles_full * pl.splits;
+    gp.total_units = gp.full_units;
+  }
   gp.a_bytes = pl.a_bytes; gp.b_bytes = pl.b_bytes; gp.stage_bytes = pl.stage_bytes;
   gp.a_exact = pl.a_exact; gp.b_exact = pl.b_exact;
   gp.a_tail_off = pl.a_bytes + pl.b_bytes;
@@ -1096,11 +1205,11 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   if (const char* dbg = getenv("RTDC_GEMM_DEBUG_BUF")) gp.dbg_times = reinterpret_cast<long long*>(strtoull(dbg, nullptr, 0));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool three = d->precision == 3;
-  rc = dispatch(d, three, ta, tb, to, gp, pl, st);
+  rc = dispatch(d, three, ta, tb, to, ta3, tb3, gp, pl, st);
   if (rc != RTDC_OK) return rc;
   if (pl.splits > 1) {
     dim3 grid(pl.m_tiles * pl.n_tiles * ((pl.bn + 31) / 32), BM / 32);
-    splitk_reduce_kernel<<<grid, 256, 0, st>>>(gp.scratch, pl.splits, pl.m_tiles, pl.bn, d->M, d->N, n_store, d->out, d->ldo,
+    splitk_reduce_kernel<<<grid, 256, 0, st>>>(gp.scratch, pl.splits, pl.splits_last, pl.n_tiles, pl.m_tiles, pl.bn, d->M, d->N, n_store, d->out, d->ldo,
                                               d->bias, d->relu, gp.alpha, d->row_bias, d->row_bias_scale);
     RTDC_CUDA_CHECK(cudaGetLastError());
   }
@@ -1108,15 +1217,15 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
 }
 
 static int dispatch(const rtdc_gemm_desc* d, bool three, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
-                    const rtdc::GemmParams& gp, const rtdc::Plan& pl, cudaStream_t st) {
+                    const CUtensorMap& ta3, const CUtensorMap& tb3, const rtdc::GemmParams& gp, const rtdc::Plan& pl, cudaStream_t st) {
   if (pl.two_cta) {
-    if (!d->a_mn && !d->b_mn) return launch_2cta<false, false>(ta, tb, to, gp, pl, st);
-    if (!d->a_mn && d->b_mn)  return launch_2cta<false, true>(ta, tb, to, gp, pl, st);
-    if (d->a_mn && !d->b_mn)  return launch_2cta<true, false>(ta, tb, to, gp, pl, st);
-    return launch_2cta<true, true>(ta, tb, to, gp, pl, st);
+    if (!d->a_mn && !d->b_mn) return launch_2cta<false, false>(ta, tb, to, ta3, tb3, gp, pl, st);
+    if (!d->a_mn && d->b_mn)  return launch_2cta<false, true>(ta, tb, to, ta3, tb3, gp, pl, st);
+    if (d->a_mn && !d->b_mn)  return launch_2cta<true, false>(ta, tb, to, ta3, tb3, gp, pl, st);
+    return launch_2cta<true, true>(ta, tb, to, ta3, tb3, gp, pl, st);
   }
-  if (!d->a_mn && !d->b_mn) return three ? launch<false, false, 3, 16>(ta, tb, to, gp, pl, st) : launch<false, false, 1, 32>(ta, tb, to, gp, pl, st);
-  if (!d->a_mn && d->b_mn)  return three ? launch<false, true, 3, 16>(ta, tb, to, gp, pl, st)  : launch<false, true, 1, 32>(ta, tb, to, gp, pl, st);
-  if (d->a_mn && !d->b_mn)  return three ? launch<true, false, 3, 16>(ta, tb, to, gp, pl, st)  : launch<true, false, 1, 32>(ta, tb, to, gp, pl, st);
-  return three ? launch<true, true, 3, 16>(ta, tb, to, gp, pl, st) : launch<true, true, 1, 32>(ta, tb, to, gp, pl, st);
+  if (!d->a_mn && !d->b_mn) return three ? launch<false, false, 3, 16>(ta, tb, to, ta3, tb3, gp, pl, st) : launch<false, false, 1, 32>(ta, tb, to, ta3, tb3, gp, pl, st);
+  if (!d->a_mn && d->b_mn)  return three ? launch<false, true, 3, 16>(ta, tb, to, ta3, tb3, gp, pl, st)  : launch<false, true, 1, 32>(ta, tb, to, ta3, tb3, gp, pl, st);
+  if (d->a_mn && !d->b_mn)  return three ? launch<true, false, 3, 16>(ta, tb, to, ta3, tb3, gp, pl, st)  : launch<true, false, 1, 32>(ta, tb, to, ta3, tb3, gp, pl, st);
+  return three ? launch<true, true, 3, 16>(ta, tb, to, ta3, tb3, gp, pl, st) : launch<true, true, 1, 32>(ta, tb, to, ta3, tb3, gp, pl, st);
 }
