@@ -89,6 +89,45 @@ __device__ __forceinline__ uint32_t rand16(const Philox4& r, int j) {
   return (j & 1) ? (w >> 16) : (w & 0xFFFFu);
 }
 
+// Dropout keep flags of 32 consecutive elements of one row (bit q = keep column col0 + q). Element index e = row*N + col,
+// 8 elements per Philox call, 16 bits each.
+__device__ __forceinline__ uint32_t dropout_keep_bits(const GemmParams& p, int row, int col0, uint32_t step) {
+  const unsigned long long e_base = static_cast<unsigned long long>(row) * static_cast<unsigned long long>(p.N) + col0;
+  uint32_t bits = 0;
+  if ((e_base & 7ull) == 0ull) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const unsigned long long grp = (e_base >> 3) + g;
+      const Philox4 rnd = philox4x32_10(static_cast<uint32_t>(grp), static_cast<uint32_t>(grp >> 32), step, p.salt, p.seed_lo, p.seed_hi);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) bits |= (rand16(rnd, q) >= p.drop_thr16 ? 1u : 0u) << (g * 8 + q);
+    }
+  } else {
+    // unaligned row start (N not a multiple of 8): one Philox call per element (rare shapes only)
+#pragma unroll 1
+    for (int q = 0; q < 32; ++q) {
+      const unsigned long long e = e_base + q, grp = e >> 3;
+      const Philox4 rnd = philox4x32_10(static_cast<uint32_t>(grp), static_cast<uint32_t>(grp >> 32), step, p.salt, p.seed_lo, p.seed_hi);
+      bits |= (rand16(rnd, static_cast<int>(e & 7ull)) >= p.drop_thr16 ? 1u : 0u) << q;
+    }
+  }
+  return bits;
+}
+// The keep flags of a whole unit (up to eight 32-column chunks), computed by the epilogue warps while they wait for the
+// accumulators, so that the Philox rounds are off the critical path between the last MMA and the last store.
+struct KeepBits { uint32_t w[8]; };
+__device__ __forceinline__ uint32_t keep_word(const KeepBits& k, int c) {
+  uint32_t r = k.w[0];
+#pragma unroll
+  for (int i = 1; i < 8; ++i) r = (c == i) ? k.w[i] : r;
+  return r;
+}
+__device__ __forceinline__ void precompute_keep_bits(const GemmParams& p, int row, int n0, uint32_t step, KeepBits& k) {
+  const int n_chunks = (min(p.bn, p.n_store - n0) + 31) / 32;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) k.w[c] = (c < n_chunks && row < p.M) ? dropout_keep_bits(p, row, n0 + c * 32, step) : 0u;
+}
+
 // Epilogue of one work unit, run by the four epilogue warps: TMEM -> registers -> (+bias, ReLU, dropout,
 // backward mask) -> swizzled smem box -> TMA store (or split-K partial to scratch). `release()` hands the
 // accumulator buffer back to the MMA issuer right after this warp's last TMEM read. `part` selects the 32-column
@@ -98,7 +137,7 @@ template <class ReleaseFn>
 __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtensorMap* tmOut, uint32_t taddr, int umma_n,
                                               int tile, int split, int m0, int n0, int r_in_tile, int lane, int wq,
                                               const float* s_bias, uint8_t* stage_buf, uint32_t& stores_issued,
-                                              uint32_t step, ReleaseFn release, int part = 0) {
+                                              uint32_t step, ReleaseFn release, int part = 0, const KeepBits* keep = nullptr) {
   const bool has_drop = p.drop_thr16 != 0u;
   const bool has_mask = p.mask_src != nullptr;
   const bool relu = p.relu != 0;
@@ -132,7 +171,8 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
   // backward mask of chunk 0 (the loads of chunk c+1 are issued while chunk c is being processed)
   const bool mask_vec_ok = has_mask && row < p.M && ((reinterpret_cast<uintptr_t>(p.mask_src) & 15u) == 0) && (p.ldm & 3) == 0 &&
                            (n0 & 3) == 0;
-  const int c_half = (n_chunks + 1) >> 1;
+  // the epilogue warps arrive with their dropout flags precomputed, the helping splitter warps do not: 5/8 vs 3/8
+  const int c_half = has_drop ? (5 * n_chunks + 7) >> 3 : (n_chunks + 1) >> 1;
   const int c_begin = part == 2 ? c_half : 0, c_end = part == 1 ? c_half : n_chunks;
   float4 mk[8];
   if (mask_vec_ok && c_begin < c_end && n0 + c_begin * 32 + 32 <= p.N) {
@@ -182,31 +222,11 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
       }
     }
     const int col0 = n0 + c * 32;
-    // dropout: element index e = row*N + col, 8 elements per Philox call, 16 bits each
+    // dropout (flags precomputed by the caller while it waited for the accumulators, or computed here)
     if (has_drop && row < p.M) {
+      const uint32_t bits = keep != nullptr ? keep_word(*keep, c) : dropout_keep_bits(p, row, col0, step);
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const unsigned long long e0 =
-            static_cast<unsigned long long>(row) * static_cast<unsigned long long>(p.N) + (col0 + g * 8);
-        if ((e0 & 7ull) == 0ull) {
-          const unsigned long long grp = e0 >> 3;
-          const Philox4 rnd = philox4x32_10(static_cast<uint32_t>(grp), static_cast<uint32_t>(grp >> 32), step,
-                                            p.salt, p.seed_lo, p.seed_hi);
-#pragma unroll
-          for (int q = 0; q < 8; ++q)
-            v[g * 8 + q] = (rand16(rnd, q) >= p.drop_thr16) ? v[g * 8 + q] * p.drop_scale : 0.f;
-        } else {
-          // unaligned row start (N not a multiple of 8): one Philox call per element group it touches
-          for (int q = 0; q < 8; ++q) {
-            const unsigned long long e = e0 + q;
-            const unsigned long long grp = e >> 3;
-            const Philox4 rnd = philox4x32_10(static_cast<uint32_t>(grp), static_cast<uint32_t>(grp >> 32),
-                                              step, p.salt, p.seed_lo, p.seed_hi);
-            v[g * 8 + q] = (rand16(rnd, static_cast<int>(e & 7ull)) >= p.drop_thr16) ? v[g * 8 + q] * p.drop_scale
-                                                                                   : 0.f;
-          }
-        }
-      }
+      for (int q = 0; q < 32; ++q) v[q] = ((bits >> q) & 1u) ? v[q] * p.drop_scale : 0.f;
     }
     // backward mask of the previous layer's ReLU+dropout output
     if (has_mask && row < p.M) {
@@ -537,13 +557,17 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       named_bar_sync(1, EPI_THREADS);
       for (int c = et; c < MAX_BN; c += EPI_THREADS)
         s_bias[c] = (p.bias != nullptr && c < p.bn && n0 + c < p.N) ? __ldg(p.bias + n0 + c) : 0.f;
+      // dropout flags first (idle time), then the barrier: on the final unit it also waits for the splitter warps
+      KeepBits kb;
+      const bool pre = p.drop_thr16 != 0u && p.splits == 1;
+      if (pre) precompute_keep_bits(p, m0 + r_in_tile, n0, step, kb);
       if (shared) named_bar_sync(2, SPLIT_THREADS + EPI_THREADS); else named_bar_sync(1, EPI_THREADS);
 
       mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);
       tcgen05_fence_after();
 
       epilogue_unit(p, &tmOut, taddr, umma_n, tile, split, m0, n0, r_in_tile, lane, wq, s_bias, stage_buf, stores_issued, step,
-                    [&]() { if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]); }, shared ? 1 : 0);
+                    [&]() { if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]); }, shared ? 1 : 0, pre ? &kb : nullptr);
     }
     if (p.tma_store && lane == 0) tma_store_wait_all();  // smem must outlive the bulk reads
   }
@@ -815,12 +839,16 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       named_bar_sync(1, EPI_THREADS);
       for (int c = et; c < MAX_BN; c += EPI_THREADS)
         s_bias[c] = (p.bias != nullptr && c < p.bn && n0 + c < p.N) ? __ldg(p.bias + n0 + c) : 0.f;
+      // dropout flags first (idle time), then the barrier: on the final unit it also waits for the splitter warps
+      KeepBits kb;
+      const bool pre = p.drop_thr16 != 0u && p.splits == 1;
+      if (pre) precompute_keep_bits(p, m0 + r_in_tile, n0, step, kb);
       if (shared) named_bar_sync(2, SPLIT_THREADS + EPI_THREADS); else named_bar_sync(1, EPI_THREADS);
       mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);
       tcgen05_fence_after();
       if (stamps && et == 0) { if (j == 0) stamps[1] = clock64(); stamps[3] = clock64(); }
       epilogue_unit(p, &tmOut, taddr, umma_n, tile128, split, m0, n0, r_in_tile, lane, wq, s_bias, stage_buf, stores_issued, step,
-                    [&]() { if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[buf], 0); }, shared ? 1 : 0);
+                    [&]() { if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[buf], 0); }, shared ? 1 : 0, pre ? &kb : nullptr);
       if (stamps && et == 0) { if (j == 0) stamps[2] = clock64(); stamps[4] = clock64(); }
     }
     if (p.tma_store && lane == 0) tma_store_wait_all();
