@@ -121,6 +121,8 @@ def run_ours(args):
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}; launch with torch.distributed.run --nproc-per-node {args.gpus}")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    from ray_torch_distributed_checkpoint_b200.utils.affinity import bind_to_gpu_numa
+    numa = bind_to_gpu_numa(local)                           # pinned input buffers next to this GPU's PCIe root port
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)      # control plane + max-over-ranks only
     ops.load_library()
@@ -216,7 +218,7 @@ def run_ours(args):
         "config": {"model": MODEL, "global_batch": global_batch, "batch_per_gpu": B, "seq_len": None,
                    "parallelism": f"dp{world}", "l2_policy": f"no flush: inputs rotate over {rot} device batches and the "
                    f"per-step working set (~{int(B * (784 * 5 + 512 * 16 + 128) / 1e6)} MB of activations) exceeds the 126 MB L2",
-                   "allreduce": args.algo, "cuda_graph": True},
+                   "allreduce": f"{args.algo}/{eng.ar_mode}", "cuda_graph": True, "host": {"numa": numa, "cpu_count": os.cpu_count()}},
         "clocks": clk.summary(),
         "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "ms_per_step": round(e2e_ms / K, 4),
                 "h2d_bytes_per_step": B * (784 + 8), "d2h_bytes_per_step": 4,

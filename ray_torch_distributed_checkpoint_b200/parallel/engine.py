@@ -40,7 +40,8 @@ class MLPTrainEngine:
     def __init__(self, model: Optional[NeuralNetwork] = None, *, batch_size: int, lr: float = 1e-3, momentum: float = 0.9,
                  weight_decay: float = 0.0, device=None, seed: int = 0x5EED, precision: int = ops.PRECISION_FP32,
                  use_graph: bool = True, process_group=None, distributed: Optional[bool] = None, algo: str = "auto",
-                 input_mean: float = 0.5, input_std: float = 0.5, fused_head: bool = True, fold_input: bool = True):
+                 input_mean: float = 0.5, input_std: float = 0.5, fused_head: bool = True, fold_input: bool = True,
+                 ar_mode: Optional[str] = None, ar_overlap_blocks: Optional[int] = None):
         self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
         if self.device.type == "cuda" and self.device.index is None:
             self.device = torch.device("cuda", torch.cuda.current_device())
@@ -74,6 +75,12 @@ class MLPTrainEngine:
         self.rank = dist.get_rank(process_group) if self.world > 1 else 0
         self.group = process_group
         self.algo = algo
+        import os as _os
+        # "bucketed": each DDP bucket is reduced on the comm stream as soon as its last gradient exists (overlaps the rest
+        # of backward); "merged": one all-reduce of the whole gradient arena after backward (no kernel shares the SMs with
+        # the GEMMs, one latency instead of two). ar_overlap_blocks caps the grid of an overlapped bucket reduction.
+        self.ar_mode = ar_mode or _os.environ.get("RTDC_AR_MODE", "merged")
+        self.ar_overlap_blocks = int(_os.environ.get("RTDC_AR_OVERLAP_BLOCKS", "0")) if ar_overlap_blocks is None else ar_overlap_blocks
 
         # ---- arenas (bucket order == torch DDP's for this model)
         named = [(n, p) for n, p in model.named_parameters()]
@@ -158,15 +165,15 @@ class MLPTrainEngine:
         torch.cuda.current_stream().synchronize()
         stage.zero_()
 
-    def _reduce_bucket(self, b: int, main: torch.cuda.Stream):
-        if self.world == 1:
+    def _reduce_bucket(self, b: int, main: torch.cuda.Stream, last: bool = False):
+        if self.world == 1 or self.ar_mode == "merged":
             return
         bk = self.buckets[b]
         ev = torch.cuda.Event()
         ev.record(main)
         self.comm_stream.wait_event(ev)
         self.symm.all_reduce(self.g_off + bk.offset * 4, bk.numel, scale=1.0 / self.world, algo=self.algo,
-                             stream=self.comm_stream)
+                             max_blocks=0 if last else self.ar_overlap_blocks, stream=self.comm_stream)
 
     # ------------------------------------------------------------------------------------------ the step
     def _convert_input(self, src_u8: torch.Tensor, slot: int, s, paced: bool) -> int:
@@ -237,8 +244,10 @@ class MLPTrainEngine:
             ops.linear_wgrad(self.dh1, x, out=self.dW[0], precision=prec, stream=s); n += 2
         for b in range(len(self.buckets)):
             if b not in launched:
-                self._reduce_bucket(b, s); n += self.world > 1
-        if self.world > 1:
+                self._reduce_bucket(b, s, last=True); n += self.world > 1
+        if self.world > 1 and self.ar_mode == "merged":
+            self.symm.all_reduce(self.g_off, self.total, scale=1.0 / self.world, algo=self.algo, stream=s)
+        elif self.world > 1:
             s.wait_stream(self.comm_stream)
         ops.sgd_step(self.p_arena, self.g_arena, self.m_arena, self.sgd, stream=s); n += 1
         ops.counter_advance(self.step_counter, self.sgd, stream=s); n += 1

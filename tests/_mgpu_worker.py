@@ -124,22 +124,26 @@ def check_ddp(rank, world, dev):
 def check_engine(rank, world, dev):
     from ray_torch_distributed_checkpoint_b200.models import NeuralNetwork
     from ray_torch_distributed_checkpoint_b200.parallel.engine import MLPTrainEngine
-    torch.manual_seed(3 + rank)
     B = 512
-    eng = MLPTrainEngine(NeuralNetwork(), batch_size=B, lr=0.05, device=dev, seed=11)
-    # single-process restatement: same global batch on one engine without dropout differences -> use p=0 models
-    losses = []
-    for step in range(6):
-        g = torch.Generator(device=dev).manual_seed(50 * step + rank)
-        x = torch.randint(0, 256, (B, 784), dtype=torch.uint8, device=dev, generator=g)
-        y = torch.randint(0, 10, (B,), device=dev, generator=g)
-        losses.append(eng.step(x, y).item())
-    ws = [torch.empty_like(eng.p_arena) for _ in range(world)]
-    dist.all_gather(ws, eng.p_arena)
-    assert all(torch.equal(ws[0], w) for w in ws), "engine replicas diverged"
-    assert list(eng.model_state_dict())[0].startswith("module.")
-    assert losses[-1] == losses[-1]
-    eng.close()
+    finals = {}
+    for mode in ("merged", "bucketed"):
+        torch.manual_seed(3 + rank)
+        eng = MLPTrainEngine(NeuralNetwork(), batch_size=B, lr=0.05, device=dev, seed=11, ar_mode=mode)
+        losses = []
+        for step in range(6):
+            g = torch.Generator(device=dev).manual_seed(50 * step + rank)
+            x = torch.randint(0, 256, (B, 784), dtype=torch.uint8, device=dev, generator=g)
+            y = torch.randint(0, 10, (B,), device=dev, generator=g)
+            losses.append(eng.step(x, y).item())
+        ws = [torch.empty_like(eng.p_arena) for _ in range(world)]
+        dist.all_gather(ws, eng.p_arena)
+        assert all(torch.equal(ws[0], w) for w in ws), f"engine replicas diverged ({mode})"
+        assert list(eng.model_state_dict())[0].startswith("module.")
+        assert losses[-1] == losses[-1]
+        finals[mode] = eng.p_arena.clone()
+        eng.close()
+    # one all-reduce of the whole arena or one per bucket: same rank-order sums, same parameters
+    assert torch.equal(finals["merged"], finals["bucketed"]), "merged and bucketed gradient reductions disagree"
     if rank == 0:
         print(f"[mgpu] engine ok (losses {losses[0]:.4f} -> {losses[-1]:.4f})", flush=True)
 
