@@ -142,8 +142,9 @@ def check_engine(rank, world, dev):
         assert losses[-1] == losses[-1]
         finals[mode] = eng.p_arena.clone()
         eng.close()
-    # one all-reduce of the whole arena or one per bucket: same rank-order sums, same parameters
-    assert torch.equal(finals["merged"], finals["bucketed"]), "merged and bucketed gradient reductions disagree"
+    # one all-reduce of the whole arena or one per bucket: the same sums (the in-switch NVLS reduction need not add in
+    # the same order for both, so compare to rounding rather than bit for bit)
+    assert torch.allclose(finals["merged"], finals["bucketed"], rtol=1e-5, atol=1e-7), "merged and bucketed reductions disagree"
     if rank == 0:
         print(f"[mgpu] engine ok (losses {losses[0]:.4f} -> {losses[-1]:.4f})", flush=True)
 
