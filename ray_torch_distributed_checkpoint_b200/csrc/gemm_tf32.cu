@@ -590,12 +590,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 //   empty[s]  per CTA   : tcgen05.commit multicast to both    (issuer -> both producers)
 //   tmem_full per CTA   : tcgen05.commit multicast to both    (issuer -> both epilogues)
 //   tmem_empty leader   : 8 arrivals                          (both epilogues -> issuer)
-template <bool A_MN, bool B_MN>
+template <bool A_MN, bool B_MN, int BK>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                         const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmA3,
                         const __grid_constant__ CUtensorMap tmB3, const GemmParams p) {
-  constexpr int BK = 16;
   extern __shared__ uint8_t smem_dyn[];
   __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t ready_bar[MAX_STAGES];
@@ -701,8 +700,9 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       constexpr uint32_t mn_box = 128u * BK;
       const uint32_t a_lbo = A_MN ? mn_box : 16u, b_lbo = B_MN ? mn_box : 16u;
       const uint32_t a_sbo = A_MN ? 512u : kmajor_sbo, b_sbo = B_MN ? 512u : kmajor_sbo;
-      const uint32_t a_lt = A_MN ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW64;
-      const uint32_t b_lt = B_MN ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW64;
+      constexpr uint32_t kmajor_lt = BK == 32 ? UMMA_LAYOUT_SW128 : UMMA_LAYOUT_SW64;
+      const uint32_t a_lt = A_MN ? UMMA_LAYOUT_SW128_BASE32B : kmajor_lt;
+      const uint32_t b_lt = B_MN ? UMMA_LAYOUT_SW128_BASE32B : kmajor_lt;
       const uint32_t a_kstep = A_MN ? 1024u : 32u, b_kstep = B_MN ? 1024u : 32u;
       int s = 0;
       uint32_t ph = 0;
@@ -718,9 +718,12 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
         mbar_wait(&tmem_empty_bar[buf], ((j >> 1) & 1) ^ 1u);
         tcgen05_fence_after();
         const uint32_t tmem_acc = tmem_base + static_cast<uint32_t>(buf) * MAX_BN;
+        long long t_wait = 0, t_issue = 0, t_commit = 0;   // issuer time split (stamps only)
         for (int it = 0; it < n_iters; ++it) {
+          const long long c0 = stamps ? clock64() : 0;
           mbar_wait(&ready_bar[s], ph);
-          tcgen05_fence_after();
+          if (p.debug & 128) tcgen05_fence_after();   // not needed: the operands are shared memory (TMA tx + proxy-fenced tails), not TMEM
+          const long long c1 = stamps ? clock64() : 0;
           const uint32_t sa = ring + static_cast<uint32_t>(s) * p.stage_bytes;
           const uint32_t sb = sa + p.a_bytes;
           const int k_left = p.K - (kb_begin + it) * BK;
@@ -741,11 +744,13 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
             }
             umma_tf32_ss_2cta(tmem_acc, da, db, idesc, acc);
           }
+          const long long c2 = stamps ? clock64() : 0;
           tcgen05_commit_2cta(&empty_bar[s], 0x3);        // both CTAs' slots are free once these MMAs have read them
+          if (stamps) { const long long c3 = clock64(); t_wait += c1 - c0; t_issue += c2 - c1; t_commit += c3 - c2; }
           if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
         tcgen05_commit_2cta(&tmem_full_bar[buf], 0x3);    // both halves of the accumulator are complete
-        if (stamps) { if (j == 0) stamps[8] = clock64(); stamps[9] = clock64(); }
+        if (stamps) { if (j == 0) stamps[8] = clock64(); stamps[9] = clock64(); stamps[10] = t_wait; stamps[11] = t_issue; stamps[12] = t_commit; stamps[13] = n_iters; }
       }
     }
     __syncwarp();
@@ -1019,7 +1024,10 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
   pl->n_tiles = ceil_div(d->N, bn);
   if (d->n_store > d->N && d->n_store > pl->n_tiles * bn)
     return fail(RTDC_ERR_ARG, "n_store (%d) reaches beyond the last N tile", d->n_store);
-  pl->bk = d->precision == 3 ? 16 : 32;
+  // K block: the 1-CTA 3xTF32 kernel needs 16 to fit four stages of raw + tail tiles; a CTA pair stages half of B, so 32
+  // fits three (and halves the per-stage barrier / commit overhead of the issuer thread). RTDC_GEMM_2CTA_BK=16 forces 16.
+  const char* envbk = getenv("RTDC_GEMM_2CTA_BK");
+  pl->bk = d->precision == 3 ? ((two_cta && !(envbk && atoi(envbk) == 16)) ? 32 : 16) : 32;
   pl->num_kb = ceil_div(d->K, pl->bk);
   pl->a_bytes = BM * pl->bk * 4;
   pl->b_bytes = static_cast<uint32_t>(two_cta ? bn / 2 : bn) * pl->bk * 4;   // a CTA of a pair stages half of B
@@ -1092,16 +1100,23 @@ static size_t scratch_bytes_for(const Plan& pl) {
   return tiles * pl.splits * (static_cast<size_t>(BM) * MAX_BN * 4);
 }
 
-template <bool A_MN, bool B_MN>
-static int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& ta3, const CUtensorMap& tb3,
+template <bool A_MN, bool B_MN, int BK>
+static int launch_2cta_bk(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& ta3, const CUtensorMap& tb3,
                        const GemmParams& gp, const Plan& pl, cudaStream_t st) {
-  auto kern = gemm_tf32x3_2cta_kernel<A_MN, B_MN>;
+  auto kern = gemm_tf32x3_2cta_kernel<A_MN, B_MN, BK>;
   RTDC_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT - STATIC_SMEM_RESERVE));
   const int units = gp.total_units;
   const int pairs = units < num_sms() / 2 ? units : num_sms() / 2;   // persistent: one CTA pair per TPC
   kern<<<2 * pairs, NUM_THREADS, pl.smem, st>>>(ta, tb, to, ta3, tb3, gp);
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;
+}
+
+template <bool A_MN, bool B_MN>
+static int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& ta3, const CUtensorMap& tb3,
+                       const GemmParams& gp, const Plan& pl, cudaStream_t st) {
+  return pl.bk == 32 ? launch_2cta_bk<A_MN, B_MN, 32>(ta, tb, to, ta3, tb3, gp, pl, st)
+                     : launch_2cta_bk<A_MN, B_MN, 16>(ta, tb, to, ta3, tb3, gp, pl, st);
 }
 
 template <bool A_MN, bool B_MN, int NSPLIT, int BK>

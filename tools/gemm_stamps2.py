@@ -26,3 +26,6 @@ for case in (sys.argv[1:] or list(cases)):
     f = lambda col, m=None: f"{rel[:, col][m].mean():.1f}" if m is not None else f"{rel[:, col].mean():.1f}"
     print(f"{case}: {n} CTAs span {(t[:, 6].max() - t[:, 7].min()) / 1000:.1f} us | epi0 {f(1)}->{f(2)}  epiLast {f(3)}->{f(4)}  end {f(5)} | "
           f"issuer first unit done {f(8, lead)} last {f(9, lead)}", flush=True)
+    n_it = t[lead][:, 13].mean()
+    print(f"    issuer, last unit, cycles per stage over {n_it:.0f} stages: wait ready {t[lead][:, 10].mean() / n_it:.0f}  "
+          f"issue MMAs {t[lead][:, 11].mean() / n_it:.0f}  commit {t[lead][:, 12].mean() / n_it:.0f}", flush=True)
