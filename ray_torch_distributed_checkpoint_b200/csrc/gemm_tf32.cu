@@ -604,9 +604,11 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
   __shared__ uint32_t tmem_base_slot;
   __shared__ __align__(16) float s_bias[MAX_BN];
 
-  const int warp = threadIdx.x >> 5;
+  // warp index / cluster rank through a shuffle: tells the compiler they are warp-uniform, so role code stays in uniform
+  // registers (what the MMA issue path needs)
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();
+  const uint32_t rank = __shfl_sync(0xffffffffu, cluster_ctarank(), 0);
   const int pair = blockIdx.x >> 1;
   const int num_pairs = gridDim.x >> 1;
 
@@ -642,7 +644,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
   __syncthreads();
   cluster_sync_all();   // the peer's barriers are initialised before anybody arrives on them remotely
   tcgen05_fence_after();
-  const uint32_t tmem_base = tmem_base_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_slot, 0);
 
   const int total_units = p.total_units;
   const int half_bn = p.bn >> 1;
@@ -694,7 +696,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (leader CTA only)
-    if (lane == 0 && rank == 0) {
+    if (rank == 0) {   // the whole warp walks the loop (uniform control flow); one elected lane issues
       const bool a_exact = p.a_exact != 0, b_exact = p.b_exact != 0;
       constexpr uint32_t kmajor_sbo = 8u * BK * 4u;
       constexpr uint32_t mn_box = 128u * BK;
@@ -722,12 +724,14 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
         for (int it = 0; it < n_iters; ++it) {
           const long long c0 = stamps ? clock64() : 0;
           mbar_wait(&ready_bar[s], ph);
+          __syncwarp();
           if (p.debug & 128) tcgen05_fence_after();   // not needed: the operands are shared memory (TMA tx + proxy-fenced tails), not TMEM
           const long long c1 = stamps ? clock64() : 0;
           const uint32_t sa = ring + static_cast<uint32_t>(s) * p.stage_bytes;
           const uint32_t sb = sa + p.a_bytes;
           const int k_left = p.K - (kb_begin + it) * BK;
           const int ksteps = min(BK / UMMA_K, (k_left + UMMA_K - 1) / UMMA_K);
+          if (elect_one()) {
           for (int k = 0; k < ((p.debug & 2) ? 0 : ksteps); ++k) {
             const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, a_sbo, a_lt);
             const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, b_sbo, b_lt);
@@ -747,10 +751,15 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
           const long long c2 = stamps ? clock64() : 0;
           tcgen05_commit_2cta(&empty_bar[s], 0x3);        // both CTAs' slots are free once these MMAs have read them
           if (stamps) { const long long c3 = clock64(); t_wait += c1 - c0; t_issue += c2 - c1; t_commit += c3 - c2; }
+          }
+          __syncwarp();
           if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
-        tcgen05_commit_2cta(&tmem_full_bar[buf], 0x3);    // both halves of the accumulator are complete
-        if (stamps) { if (j == 0) stamps[8] = clock64(); stamps[9] = clock64(); stamps[10] = t_wait; stamps[11] = t_issue; stamps[12] = t_commit; stamps[13] = n_iters; }
+        if (elect_one()) {
+          tcgen05_commit_2cta(&tmem_full_bar[buf], 0x3);    // both halves of the accumulator are complete
+          if (stamps) { if (j == 0) stamps[8] = clock64(); stamps[9] = clock64(); stamps[10] = t_wait; stamps[11] = t_issue; stamps[12] = t_commit; stamps[13] = n_iters; }
+        }
+        __syncwarp();
       }
     }
     __syncwarp();

@@ -253,6 +253,13 @@ __device__ __forceinline__ void tcgen05_commit_2cta(uint64_t* bar, uint16_t mask
       "h"(mask)
       : "memory");
 }
+// One lane of a converged warp (the compiler keeps values computed by the whole warp in uniform registers; issuing from
+// inside `if (lane == 0)` regions instead makes it copy every operand with R2UR in an election loop, ~150 cycles per MMA).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}\n" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void umma_tf32_ss_2cta(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                                   uint32_t accumulate) {
   asm volatile(

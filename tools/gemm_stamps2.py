@@ -11,6 +11,8 @@ cases = {"fwd1": lambda: ops.gemm(x, w1, out, bias=b1, relu=True, drop_p=0.25, s
          "fwd1_exact": lambda: ops.gemm(x, w1, out, bias=b1, relu=True, drop_p=0.25, seed=1, a_exact=True),
          "fwd1_exact_nodrop": lambda: ops.gemm(x, w1, out, bias=b1, relu=True, a_exact=True),
          "fwd2": lambda: ops.gemm(h, w2, out, bias=b1, relu=True, drop_p=0.25, seed=1),
+         "fwd2_bn128": lambda: ops.gemm(h, w2, out, bias=b1, relu=True, drop_p=0.25, seed=1, bn=128),
+         "fwd2_bn64": lambda: ops.gemm(h, w2, out, bias=b1, relu=True, drop_p=0.25, seed=1, bn=64),
          "dgrad2": lambda: ops.linear_dgrad(dy, w2, mask_src=h, mask_scale=4 / 3, out=out)}
 for case in (sys.argv[1:] or list(cases)):
     os.environ.pop("RTDC_GEMM_DEBUG_BUF", None)
