@@ -70,6 +70,12 @@ typedef struct rtdc_gemm_desc {
   int a_exact, b_exact;
   float alpha;
   const float* row_bias; float row_bias_scale;
+  /* optional bit-packed activation mask. mask_bits_out: the epilogue also writes, for every output row, one uint32 per 32
+   * columns with bit q = (out[m, 32w + q] > 0) to mask_bits_out[m*ld_mask_out + w] (needs no K split). mask_bits_in: the
+   * same layout consumed as the backward mask instead of mask_src (x *= bit ? mask_scale : 0): a dgrad then reads
+   * 1/32 of the bytes of the activation it masks with. Leading dimensions in 32-bit words, >= ceil(N/32). */
+  uint32_t* mask_bits_out; int ld_mask_out;
+  const uint32_t* mask_bits_in; int ld_mask_in;
 } rtdc_gemm_desc;
 
 /* out[n] = bias[n] (0 when NULL) + t * sum_k w[n*ldw + k], n < rows: the effective bias of a Linear layer whose input

@@ -31,8 +31,11 @@ constexpr int UMMA_K = 8;         // tf32: 32 bytes per instruction along K
 constexpr int MAX_STAGES = 6;
 constexpr int MAX_BN = 256;
 constexpr int TMEM_COLS = 512;      // two 256-column accumulator buffers (epilogue of one tile overlaps the next main loop)
-constexpr int NUM_THREADS = 320;    // 10 warps: 0 TMA producer, 1 MMA issuer, 2-5 splitters, 6-9 epilogue
-constexpr int SPLIT_THREADS = 128;
+// 12 warps: 0 TMA producer, 1 MMA issuer, 2-7 splitters, 8-11 epilogue. Registers are allocated in groups of four warps, so
+// a 10-warp CTA is charged for 12 (168 registers per thread either way): the two extra warps are free splitter throughput.
+constexpr int NUM_THREADS = 384;
+constexpr int SPLIT_THREADS = 192;
+constexpr int HELP_THREADS = 128;   // splitter warps 2-5 (one per TMEM lane quarter) also take part of the final epilogue
 constexpr int EPI_THREADS = 128;
 constexpr int EPI_STAGING_BYTES = 32768;  // 4 epilogue warps x two 32x32 fp32 TMA-store boxes
 constexpr int SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
@@ -62,6 +65,8 @@ struct GemmParams {
   // MN-major operands: tiles that lie inside the first a3_limit / b3_limit rows (whole 32-element blocks) are loaded by
   // ONE 3-D TMA instruction ([blocks][k][32]) instead of one 2-D box per 32 rows; 0 = no 3-D map
   int a3_limit, b3_limit;
+  uint32_t* mask_bits_out; int ld_mask_out;        // bit-packed (out > 0), one word per 32 columns
+  const uint32_t* mask_bits_in; int ld_mask_in;    // bit-packed backward mask (instead of mask_src)
   int tma_store;         // epilogue goes through smem + cp.async.bulk.tensor stores (tmOut valid)
   long long* dbg_times;  // RTDC_GEMM_DEBUG_BUF: per-CTA clock64 stamps [grid][8]
 };
@@ -128,6 +133,43 @@ __device__ __forceinline__ void precompute_keep_bits(const GemmParams& p, int ro
   for (int c = 0; c < 8; ++c) k.w[c] = (c < n_chunks && row < p.M) ? dropout_keep_bits(p, row, n0 + c * 32, step) : 0u;
 }
 
+// Backward-mask flags of a whole unit (bit q of word c = mask_src[row, n0 + 32c + q] > 0), also gathered while the epilogue
+// warps wait for the accumulators: the loads then have the whole main loop to land instead of one chunk's time each
+// (one chunk in flight at ~1 us of memory latency made the dgrad epilogue 14 us per unit against 6 us without a mask).
+__device__ __forceinline__ void precompute_mask_bits(const GemmParams& p, int row, int n0, KeepBits& k) {
+  const int n_chunks = (min(p.bn, p.n_store - n0) + 31) / 32;
+  const bool vec_ok = ((reinterpret_cast<uintptr_t>(p.mask_src) & 15u) == 0) && (p.ldm & 3) == 0 && (n0 & 3) == 0;
+  const float* ms = p.mask_src + static_cast<size_t>(row < p.M ? row : 0) * p.ldm + n0;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    uint32_t bits = 0;
+    if (c < n_chunks && row < p.M) {
+      if (vec_ok && n0 + c * 32 + 32 <= p.N) {
+        float4 m[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) m[q] = __ldg(reinterpret_cast<const float4*>(ms + c * 32) + q);
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          bits |= (m[q].x > 0.f ? 1u : 0u) << (4 * q) | (m[q].y > 0.f ? 2u : 0u) << (4 * q) | (m[q].z > 0.f ? 4u : 0u) << (4 * q) |
+                  (m[q].w > 0.f ? 8u : 0u) << (4 * q);
+      } else {
+#pragma unroll 1
+        for (int q = 0; q < 32; ++q)
+          if (n0 + c * 32 + q < p.N && __ldg(ms + c * 32 + q) > 0.f) bits |= 1u << q;
+      }
+    }
+    k.w[c] = bits;
+  }
+}
+
+// Bit-packed backward mask: this row's words for the unit's chunks (32 bytes instead of 1 KB of activations per thread).
+__device__ __forceinline__ void load_mask_words(const GemmParams& p, int row, int n0, KeepBits& k) {
+  const int n_chunks = (min(p.bn, p.n_store - n0) + 31) / 32;
+  const uint32_t* src = p.mask_bits_in + static_cast<size_t>(row < p.M ? row : 0) * p.ld_mask_in + (n0 >> 5);
+#pragma unroll
+  for (int c = 0; c < 8; ++c) k.w[c] = (c < n_chunks && row < p.M && n0 + c * 32 < p.N) ? __ldg(src + c) : 0u;
+}
+
 // Epilogue of one work unit, run by the four epilogue warps: TMEM -> registers -> (+bias, ReLU, dropout,
 // backward mask) -> swizzled smem box -> TMA store (or split-K partial to scratch). `release()` hands the
 // accumulator buffer back to the MMA issuer right after this warp's last TMEM read. `part` selects the 32-column
@@ -137,9 +179,10 @@ template <class ReleaseFn>
 __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtensorMap* tmOut, uint32_t taddr, int umma_n,
                                               int tile, int split, int m0, int n0, int r_in_tile, int lane, int wq,
                                               const float* s_bias, uint8_t* stage_buf, uint32_t& stores_issued,
-                                              uint32_t step, ReleaseFn release, int part = 0, const KeepBits* keep = nullptr) {
+                                              uint32_t step, ReleaseFn release, int part = 0, const KeepBits* keep = nullptr,
+                                              const KeepBits* mask_bits = nullptr) {
   const bool has_drop = p.drop_thr16 != 0u;
-  const bool has_mask = p.mask_src != nullptr;
+  const bool has_mask = p.mask_src != nullptr || p.mask_bits_in != nullptr;
   const bool relu = p.relu != 0;
   const int row = m0 + r_in_tile;
   const int n_cols_out = min(p.bn, p.n_store - n0);  // columns to write (valid + zero padding)
@@ -169,13 +212,13 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
   }
 
   // backward mask of chunk 0 (the loads of chunk c+1 are issued while chunk c is being processed)
-  const bool mask_vec_ok = has_mask && row < p.M && ((reinterpret_cast<uintptr_t>(p.mask_src) & 15u) == 0) && (p.ldm & 3) == 0 &&
+  const bool mask_vec_ok = p.mask_src != nullptr && row < p.M && ((reinterpret_cast<uintptr_t>(p.mask_src) & 15u) == 0) && (p.ldm & 3) == 0 &&
                            (n0 & 3) == 0;
   // the epilogue warps arrive with their dropout flags precomputed, the helping splitter warps do not: 5/8 vs 3/8
-  const int c_half = has_drop ? (5 * n_chunks + 7) >> 3 : (n_chunks + 1) >> 1;
+  const int c_half = (has_drop || p.mask_src != nullptr) ? (5 * n_chunks + 7) >> 3 : (n_chunks + 1) >> 1;
   const int c_begin = part == 2 ? c_half : 0, c_end = part == 1 ? c_half : n_chunks;
   float4 mk[8];
-  if (mask_vec_ok && c_begin < c_end && n0 + c_begin * 32 + 32 <= p.N) {
+  if (mask_bits == nullptr && mask_vec_ok && c_begin < c_end && n0 + c_begin * 32 + 32 <= p.N) {
     const float4* ms4 = reinterpret_cast<const float4*>(p.mask_src + static_cast<size_t>(row) * p.ldm + n0 + c_begin * 32);
 #pragma unroll
     for (int q = 0; q < 8; ++q) mk[q] = __ldg(ms4 + q);
@@ -229,7 +272,11 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
       for (int q = 0; q < 32; ++q) v[q] = ((bits >> q) & 1u) ? v[q] * p.drop_scale : 0.f;
     }
     // backward mask of the previous layer's ReLU+dropout output
-    if (has_mask && row < p.M) {
+    if (has_mask && mask_bits != nullptr) {
+      const uint32_t bits = keep_word(*mask_bits, c);
+#pragma unroll
+      for (int q = 0; q < 32; ++q) v[q] = ((bits >> q) & 1u) ? v[q] * p.mask_scale : 0.f;
+    } else if (has_mask && row < p.M) {
       const float* ms = p.mask_src + static_cast<size_t>(row) * p.ldm + col0;
       if (mask_vec_ok && col0 + 32 <= p.N) {
 #pragma unroll
@@ -249,6 +296,13 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
 #pragma unroll
         for (int q = 0; q < 8; ++q) mk[q] = __ldg(reinterpret_cast<const float4*>(ms + 32) + q);
       }
+    }
+    // bit-packed (out > 0) for a later dgrad
+    if (p.mask_bits_out != nullptr && row < p.M && col0 < p.N) {
+      uint32_t bits = 0;
+#pragma unroll
+      for (int q = 0; q < 32; ++q) bits |= (v[q] > 0.f ? 1u : 0u) << q;   // columns past N hold zeros
+      p.mask_bits_out[static_cast<size_t>(row) * p.ld_mask_out + (col0 >> 5)] = bits;
     }
     if (p.debug & 4) continue;
     if (p.tma_store) {
@@ -274,9 +328,14 @@ __device__ __forceinline__ void epilogue_unit(const GemmParams& p, const CUtenso
         // column sums of this warp's 32 x 32 box straight from the staged tile (lane = column; the swizzle
         // makes the 32 lanes hit 32 different banks): the bias gradient costs no extra pass over HBM
         const int valid = min(32, p.M - (m0 + wq * 32));
-        float cs = 0.f;
-        for (int rr = 0; rr < valid; ++rr)
-          cs += *reinterpret_cast<const float*>(box + rr * 128 + ((((lane >> 2) ^ (rr & 7))) << 4) + ((lane & 3) << 2));
+        // four independent partial sums (a single chain of 32 dependent shared loads + adds costs ~1000 cycles per chunk)
+        float c4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int rr = 0; rr < 32; ++rr) {
+          const float e = *reinterpret_cast<const float*>(box + rr * 128 + ((((lane >> 2) ^ (rr & 7))) << 4) + ((lane & 3) << 2));
+          c4[rr & 3] += rr < valid ? e : 0.f;     // rows past M hold bias-only values that the store clips
+        }
+        const float cs = (c4[0] + c4[1]) + (c4[2] + c4[3]);
         if (col0 + lane < p.N)
           p.colsum_partial[static_cast<size_t>((m0 / BM) * 4 + wq) * p.ld_colsum + col0 + lane] = cs;
       }
@@ -512,7 +571,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
     // nothing left to split: take the second half of this CTA's final epilogue (staging boxes in the idle ring)
-    if (share_final) {
+    if (share_final && warp < 2 + HELP_THREADS / 32) {
       const int n_mine = (total_units - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
       const int j = n_mine - 1, u = static_cast<int>(blockIdx.x) + j * static_cast<int>(gridDim.x);
       const Unit w = decode_unit(p, u);
@@ -526,11 +585,13 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t step = p.step_imm;
       if (p.drop_thr16 != 0u && p.step_ptr != nullptr) step = *p.step_ptr;
       uint32_t stores_issued = 0;
-      named_bar_sync(2, SPLIT_THREADS + EPI_THREADS);   // the epilogue warps have staged this unit's bias slice
+      KeepBits hmb;
+      if (p.mask_bits_in != nullptr) load_mask_words(p, m0 + wq * 32 + lane, n0, hmb);
+      named_bar_sync(2, HELP_THREADS + EPI_THREADS);   // the epilogue warps have staged this unit's bias slice
       mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);     // all MMAs done: accumulators complete, ring idle
       tcgen05_fence_after();
       epilogue_unit(p, &tmOut, taddr, umma_n, tile, split, m0, n0, wq * 32 + lane, lane, wq, s_bias, ring_ptr + static_cast<size_t>(wq) * 8192,
-                    stores_issued, step, []() {}, 2);
+                    stores_issued, step, []() {}, 2, nullptr, p.mask_bits_in != nullptr ? &hmb : nullptr);
       if (p.tma_store && lane == 0) tma_store_wait_all();
     }
   } else {
@@ -561,13 +622,18 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       KeepBits kb;
       const bool pre = p.drop_thr16 != 0u && p.splits == 1;
       if (pre) precompute_keep_bits(p, m0 + r_in_tile, n0, step, kb);
-      if (shared) named_bar_sync(2, SPLIT_THREADS + EPI_THREADS); else named_bar_sync(1, EPI_THREADS);
+      KeepBits mb;
+      const bool pre_mask = (p.mask_src != nullptr || p.mask_bits_in != nullptr) && p.splits == 1;
+      if (p.mask_bits_in != nullptr) load_mask_words(p, m0 + r_in_tile, n0, mb);
+      else if (pre_mask) precompute_mask_bits(p, m0 + r_in_tile, n0, mb);
+      if (shared) named_bar_sync(2, HELP_THREADS + EPI_THREADS); else named_bar_sync(1, EPI_THREADS);
 
       mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);
       tcgen05_fence_after();
 
       epilogue_unit(p, &tmOut, taddr, umma_n, tile, split, m0, n0, r_in_tile, lane, wq, s_bias, stage_buf, stores_issued, step,
-                    [&]() { if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]); }, shared ? 1 : 0, pre ? &kb : nullptr);
+                    [&]() { if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]); }, shared ? 1 : 0, pre ? &kb : nullptr,
+                    pre_mask ? &mb : nullptr);
     }
     if (p.tma_store && lane == 0) tma_store_wait_all();  // smem must outlive the bulk reads
   }
@@ -656,7 +722,8 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (both CTAs)
-    if (lane == 0) {
+    // the whole warp walks the loop, one elected lane issues (operands stay in uniform registers, as for the MMAs)
+    {
       int s = 0;
       uint32_t ph = 0;
       for (int u = pair; u < total_units; u += num_pairs) {
@@ -669,31 +736,37 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
         const int nb0 = n0 + static_cast<int>(rank) * (umma_n >> 1);                          // this CTA's half of it
         for (int it = 0; it < n_iters; ++it) {
           mbar_wait(&empty_bar[s], ph ^ 1u);
-          uint8_t* sa = ring_ptr + static_cast<size_t>(s) * p.stage_bytes;
-          uint8_t* sb = sa + p.a_bytes;
-          if (p.debug & 1) { mbar_arrive(&full_bar[s]); if (++s == p.stages) { s = 0; ph ^= 1u; } continue; }
-          mbar_expect_tx(&full_bar[s], p.a_bytes + p.b_bytes);
-          const int k0 = (kb_begin + it) * BK;
-          if (!A_MN) {
-            tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
-          } else if (m0 + BM <= p.a3_limit) {
-            tma_load_3d(sa, &tmA3, &full_bar[s], 0, k0, m0 >> 5);
-          } else {
+          __syncwarp();
+          if (elect_one()) {
+            uint8_t* sa = ring_ptr + static_cast<size_t>(s) * p.stage_bytes;
+            uint8_t* sb = sa + p.a_bytes;
+            if (p.debug & 1) {
+              mbar_arrive(&full_bar[s]);
+            } else {
+              mbar_expect_tx(&full_bar[s], p.a_bytes + p.b_bytes);
+              const int k0 = (kb_begin + it) * BK;
+              if (!A_MN) {
+                tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
+              } else if (m0 + BM <= p.a3_limit) {
+                tma_load_3d(sa, &tmA3, &full_bar[s], 0, k0, m0 >> 5);
+              } else {
 #pragma unroll
-            for (int b = 0; b < BM / 32; ++b) tma_load_2d(sa + b * (128 * BK), &tmA, &full_bar[s], m0 + 32 * b, k0);
+                for (int b = 0; b < BM / 32; ++b) tma_load_2d(sa + b * (128 * BK), &tmA, &full_bar[s], m0 + 32 * b, k0);
+              }
+              if (!B_MN) {
+                tma_load_2d(sb, &tmB, &full_bar[s], k0, nb0);
+              } else if (nb0 + half_bn <= p.b3_limit) {
+                tma_load_3d(sb, &tmB3, &full_bar[s], 0, k0, nb0 >> 5);
+              } else {
+                for (int b = 0; b < half_bn / 32; ++b) tma_load_2d(sb + b * (128 * BK), &tmB, &full_bar[s], nb0 + 32 * b, k0);
+              }
+            }
           }
-          if (!B_MN) {
-            tma_load_2d(sb, &tmB, &full_bar[s], k0, nb0);
-          } else if (nb0 + half_bn <= p.b3_limit) {
-            tma_load_3d(sb, &tmB3, &full_bar[s], 0, k0, nb0 >> 5);
-          } else {
-            for (int b = 0; b < half_bn / 32; ++b) tma_load_2d(sb + b * (128 * BK), &tmB, &full_bar[s], nb0 + 32 * b, k0);
-          }
+          __syncwarp();
           if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
       }
     }
-    __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (leader CTA only)
     if (rank == 0) {   // the whole warp walks the loop (uniform control flow); one elected lane issues
@@ -776,7 +849,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
         mbar_wait(&full_bar[s], ph);
         const float4* raw = reinterpret_cast<const float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes);
         float4* tail = reinterpret_cast<float4*>(ring_ptr + static_cast<size_t>(s) * p.stage_bytes + raw_bytes) - lo;
-        constexpr int SPLIT_ILP = 4;
+        constexpr int SPLIT_ILP = 8;
         for (int base = lo + st; base < ((p.debug & 8) ? 0 : nvec); base += SPLIT_THREADS * SPLIT_ILP) {
           float4 v[SPLIT_ILP];
 #pragma unroll
@@ -804,7 +877,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       }
     }
     // nothing left to split: take the second half of this CTA's final epilogue (staging boxes in the idle ring)
-    if (share_final) {
+    if (share_final && warp < 2 + HELP_THREADS / 32) {
       const int n_mine = (total_units - pair + num_pairs - 1) / num_pairs;
       const int j = n_mine - 1, u = pair + j * num_pairs;
       const Unit w = decode_unit(p, u);
@@ -821,11 +894,14 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       uint32_t step = p.step_imm;
       if (p.drop_thr16 != 0u && p.step_ptr != nullptr) step = *p.step_ptr;
       uint32_t stores_issued = 0;
-      named_bar_sync(2, SPLIT_THREADS + EPI_THREADS);   // the epilogue warps have staged this unit's bias slice
+      KeepBits hmb;
+      if (p.mask_bits_in != nullptr) load_mask_words(p, m0 + wq * 32 + lane, n0, hmb);
+      named_bar_sync(2, HELP_THREADS + EPI_THREADS);   // the epilogue warps have staged this unit's bias slice
       mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);     // the pair's MMAs are done: accumulators complete, both rings idle
       tcgen05_fence_after();
       epilogue_unit(p, &tmOut, taddr, umma_n, tile128, split, m0, n0, wq * 32 + lane, lane, wq, s_bias,
-                    ring_ptr + static_cast<size_t>(wq) * 8192, stores_issued, step, []() {}, 2);
+                    ring_ptr + static_cast<size_t>(wq) * 8192, stores_issued, step, []() {}, 2, nullptr,
+                    p.mask_bits_in != nullptr ? &hmb : nullptr);
       if (p.tma_store && lane == 0) tma_store_wait_all();
     }
   } else {
@@ -857,12 +933,17 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       KeepBits kb;
       const bool pre = p.drop_thr16 != 0u && p.splits == 1;
       if (pre) precompute_keep_bits(p, m0 + r_in_tile, n0, step, kb);
-      if (shared) named_bar_sync(2, SPLIT_THREADS + EPI_THREADS); else named_bar_sync(1, EPI_THREADS);
+      KeepBits mb;
+      const bool pre_mask = (p.mask_src != nullptr || p.mask_bits_in != nullptr) && p.splits == 1;
+      if (p.mask_bits_in != nullptr) load_mask_words(p, m0 + r_in_tile, n0, mb);
+      else if (pre_mask) precompute_mask_bits(p, m0 + r_in_tile, n0, mb);
+      if (shared) named_bar_sync(2, HELP_THREADS + EPI_THREADS); else named_bar_sync(1, EPI_THREADS);
       mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);
       tcgen05_fence_after();
       if (stamps && et == 0) { if (j == 0) stamps[1] = clock64(); stamps[3] = clock64(); }
       epilogue_unit(p, &tmOut, taddr, umma_n, tile128, split, m0, n0, r_in_tile, lane, wq, s_bias, stage_buf, stores_issued, step,
-                    [&]() { if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[buf], 0); }, shared ? 1 : 0, pre ? &kb : nullptr);
+                    [&]() { if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[buf], 0); }, shared ? 1 : 0, pre ? &kb : nullptr,
+                    pre_mask ? &mb : nullptr);
       if (stamps && et == 0) { if (j == 0) stamps[2] = clock64(); stamps[4] = clock64(); }
     }
     if (p.tma_store && lane == 0) tma_store_wait_all();
@@ -1056,7 +1137,7 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
   if (splits == 0) {
     splits = 1;
     const int sms = (need_device ? num_sms() : 148) / (two_cta ? 2 : 1);
-    if (tiles * 2 <= sms && d->K >= 512 && d->drop_p <= 0.f && d->mask_src == nullptr) {
+    if (tiles * 2 <= sms && d->K >= 512 && d->drop_p <= 0.f && d->mask_src == nullptr && d->mask_bits_in == nullptr && d->mask_bits_out == nullptr) {
       splits = sms / tiles;
       const int max_by_k = d->K / 256;  // keep >= 256 K elements per split
       if (splits > max_by_k) splits = max_by_k;
@@ -1064,7 +1145,8 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
       if (splits < 1) splits = 1;
     }
   }
-  if (splits > 1 && (d->drop_p > 0.f || d->mask_src != nullptr || d->colsum_partial != nullptr)) splits = 1;  // those epilogues need the full sum in TMEM
+  if (splits > 1 && (d->drop_p > 0.f || d->mask_src != nullptr || d->colsum_partial != nullptr || d->mask_bits_in != nullptr ||
+                     d->mask_bits_out != nullptr)) splits = 1;  // those epilogues need the full sum in TMEM
   if (splits > pl->num_kb) splits = pl->num_kb;
   pl->kb_per_split = ceil_div(pl->num_kb, splits);
   pl->splits = ceil_div(pl->num_kb, pl->kb_per_split);  // no empty split
@@ -1232,6 +1314,13 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   gp.seed_lo = static_cast<uint32_t>(d->seed); gp.seed_hi = static_cast<uint32_t>(d->seed >> 32);
   gp.step_ptr = d->step_ptr; gp.step_imm = d->step_imm; gp.salt = d->salt;
   gp.mask_src = d->mask_src; gp.ldm = d->ldm; gp.mask_scale = d->mask_scale;
+  if (d->mask_bits_in != nullptr && d->mask_src != nullptr) return fail(RTDC_ERR_ARG, "give the backward mask either as mask_src or as mask_bits_in, not both");
+  if ((d->mask_bits_in != nullptr && d->ld_mask_in * 32 < d->N) || (d->mask_bits_out != nullptr && d->ld_mask_out * 32 < d->N))
+    return fail(RTDC_ERR_ARG, "mask bit rows need at least ceil(N/32) words");
+  if ((d->mask_bits_in != nullptr || d->mask_bits_out != nullptr) && pl.n_tiles > 1 && pl.bn % 32 != 0)
+    return fail(RTDC_ERR_ARG, "bit-packed masks need N tiles that are multiples of 32 columns");
+  gp.mask_bits_out = d->mask_bits_out; gp.ld_mask_out = d->ld_mask_out;
+  gp.mask_bits_in = d->mask_bits_in; gp.ld_mask_in = d->ld_mask_in;
   if (pl.splits > 1) {
     const size_t need = scratch_bytes_for(pl);
     if (!d->scratch || d->scratch_bytes < need)

@@ -40,6 +40,8 @@ class GemmDesc(C.Structure):
         ("a_exact", C.c_int), ("b_exact", C.c_int),
         ("alpha", C.c_float),
         ("row_bias", C.c_void_p), ("row_bias_scale", C.c_float),
+        ("mask_bits_out", C.c_void_p), ("ld_mask_out", C.c_int),
+        ("mask_bits_in", C.c_void_p), ("ld_mask_in", C.c_int),
     ]
 
 

@@ -49,7 +49,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
          mask_src: Optional[torch.Tensor] = None, mask_scale: float = 1.0,
          n_store: Optional[int] = None, precision: int = PRECISION_FP32, bn: int = 0, splits: int = 0,
          colsum_partial: Optional[torch.Tensor] = None, a_exact: bool = False, b_exact: bool = False, alpha: float = 1.0,
-         row_bias: Optional[torch.Tensor] = None, row_bias_scale: float = 1.0, stream=None) -> torch.Tensor:
+         row_bias: Optional[torch.Tensor] = None, row_bias_scale: float = 1.0,
+         mask_bits_out: Optional[torch.Tensor] = None, mask_bits_in: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
     """``out[M,N] = epilogue(sum_k A(m,k) B(n,k))`` on the tensor cores.
 
     ``a`` is ``[M,K]`` (``a_mn=False``) or ``[K,M]`` (``a_mn=True``); ``b`` is ``[N,K]`` or ``[K,N]``.
@@ -57,7 +58,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
     (padded buffers). ``a_exact`` / ``b_exact`` promise that the operand's values are exact in tf32 (e.g. raw
     uint8 pixels widened to fp32) so its 3xTF32 correction pass is skipped; the accumulator is mapped as
     ``acc*alpha + bias[n] + row_bias[m]*row_bias_scale`` before the activation epilogue (input-normalisation
-    folding, see ``include/rtdc_b200.h``).
+    folding, see ``include/rtdc_b200.h``). ``mask_bits_out`` (int32 ``[M, >= ceil(N/32)]``) receives one bit per output
+    element (``out > 0``); ``mask_bits_in`` is such a tensor used as the backward mask in place of ``mask_src``.
     """
     _check(a, "a"); _check(b, "b"); _check(out, "out")
     am, ak = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
@@ -92,6 +94,14 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
         if row_bias.dtype != torch.float32 or row_bias.numel() < M or not row_bias.is_contiguous():
             raise ValueError("row_bias must be a contiguous float32 tensor with at least M elements")
         d.row_bias, d.row_bias_scale = row_bias.data_ptr(), float(row_bias_scale)
+    for name, t in (("mask_bits_out", mask_bits_out), ("mask_bits_in", mask_bits_in)):
+        if t is not None:
+            if t.dtype != torch.int32 or not t.is_cuda or t.dim() != 2 or t.stride(1) != 1 or t.shape[0] < M or t.shape[1] * 32 < N:
+                raise ValueError(f"{name} must be an int32 CUDA tensor of shape [>= M, >= ceil(N/32)] with unit inner stride")
+    if mask_bits_out is not None:
+        d.mask_bits_out, d.ld_mask_out = mask_bits_out.data_ptr(), mask_bits_out.stride(0)
+    if mask_bits_in is not None:
+        d.mask_bits_in, d.ld_mask_in, d.mask_scale = mask_bits_in.data_ptr(), mask_bits_in.stride(0), float(mask_scale)
     lib = _lib.load()
     need = lib.rtdc_gemm_scratch_bytes(C.byref(d))
     if need:
@@ -113,7 +123,8 @@ def gemm_plan(M: int, N: int, K: int, *, b_mn: bool = False, precision: int = PR
 # Linear-layer shaped helpers
 
 def linear_forward(x, weight, bias=None, *, relu=False, drop_p=0.0, seed=0, step=0, step_tensor=None, salt=0,
-                   out=None, n_store=None, precision=PRECISION_FP32, x_exact=False, alpha=1.0, stream=None):
+                   out=None, n_store=None, precision=PRECISION_FP32, x_exact=False, alpha=1.0, mask_bits_out=None,
+                   stream=None):
     """``y = dropout(relu(alpha * (x @ weight.T) + bias))`` in one kernel (K1-K3, K12). ``x_exact``: the values of
     ``x`` are exact in tf32 (raw pixels), see :func:`gemm`."""
     B, N = x.shape[0], weight.shape[0]
@@ -121,19 +132,20 @@ def linear_forward(x, weight, bias=None, *, relu=False, drop_p=0.0, seed=0, step
         out = torch.empty(B, n_store or N, dtype=torch.float32, device=x.device)
     return gemm(x, weight, out, M=B, N=N, K=weight.shape[1], bias=bias, relu=relu, drop_p=drop_p, seed=seed, step=step,
                 step_tensor=step_tensor, salt=salt, n_store=n_store, precision=precision, a_exact=x_exact, alpha=alpha,
-                stream=stream)
+                mask_bits_out=mask_bits_out, stream=stream)
 
 
 def linear_dgrad(dy, weight, *, N_out=None, mask_src=None, mask_scale=1.0, out=None, precision=PRECISION_FP32,
-                 colsum_partial=None, stream=None):
+                 colsum_partial=None, mask_bits=None, stream=None):
     """``dx = (dy @ weight) * (mask_src > 0) * mask_scale`` (K6 dgrad + ReLU/dropout backward of the
-    layer below). ``dy`` may be stored wider than ``N_out`` columns (zero padded)."""
+    layer below). ``dy`` may be stored wider than ``N_out`` columns (zero padded). ``mask_bits``: the bit-packed
+    ``(h > 0)`` a forward GEMM wrote with ``mask_bits_out``, used instead of ``mask_src``."""
     n_out = weight.shape[0] if N_out is None else N_out
     B, K_in = dy.shape[0], weight.shape[1]
     if out is None:
         out = torch.empty(B, K_in, dtype=torch.float32, device=dy.device)
     return gemm(dy, weight, out, b_mn=True, M=B, N=K_in, K=n_out, mask_src=mask_src, mask_scale=mask_scale,
-                precision=precision, colsum_partial=colsum_partial, stream=stream)
+                precision=precision, colsum_partial=colsum_partial, mask_bits_in=mask_bits, stream=stream)
 
 
 def linear_wgrad(dy, x, *, N_out=None, out=None, precision=PRECISION_FP32, splits=0, x_exact=False, alpha=1.0,

@@ -134,6 +134,7 @@ class MLPTrainEngine:
         self.dh2 = torch.empty(B, self.d_h, device=dev)
         self.dh1 = torch.empty(B, self.d_h, device=dev)
         self.dh1_colsum = torch.zeros(4 * ((B + 127) // 128), self.d_h, device=dev)
+        self.h1_bits = torch.zeros(B, (self.d_h + 31) // 32, dtype=torch.int32, device=dev)   # (h1 > 0), 1 bit per element
         self.b1_eff = torch.zeros(self.d_h, device=dev)      # b1 + t*rowsum(W1) for the folded input layer
         self.loss = torch.zeros((), device=dev)
         self.step_counter = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -193,15 +194,16 @@ class MLPTrainEngine:
         p = self.p_drop if train else 0.0
         kw = dict(seed=self.seed, step_tensor=self.step_counter, precision=self.precision, stream=s)
         x = self.x[slot]
+        kw1 = dict(kw, mask_bits_out=self.h1_bits if train else None)   # dgrad2 masks with 1 bit per element of h1
         if from_u8 and self.input_mode == "shift":
             ops.linear_forward(x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, x_exact=True,
-                               alpha=self.in_scale, **kw); n += 1
+                               alpha=self.in_scale, **kw1); n += 1
         elif from_u8 and self.input_mode == "fold":
             ops.fold_input_bias(self.W[0], self.b[0], self.in_shift, out=self.b1_eff, stream=s); n += 1
             ops.linear_forward(x, self.W[0], self.b1_eff, relu=True, drop_p=p, salt=1, out=self.h1, x_exact=True,
-                               alpha=self.in_scale, **kw); n += 1
+                               alpha=self.in_scale, **kw1); n += 1
         else:
-            ops.linear_forward(x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, **kw); n += 1
+            ops.linear_forward(x, self.W[0], self.b[0], relu=True, drop_p=p, salt=1, out=self.h1, **kw1); n += 1
         ops.linear_forward(self.h1, self.W[1], self.b[1], relu=True, drop_p=p, salt=2, out=self.h2, **kw); n += 1
         if with_logits:
             ops.linear_forward(self.h2, self.W[2], self.b[2], relu=True, out=self.z, n_store=_LOGIT_LD, **kw); n += 1
@@ -231,7 +233,7 @@ class MLPTrainEngine:
         if self.bucket_of_layer[1] != self.bucket_of_layer[0]:
             self._reduce_bucket(self.bucket_of_layer[1], s); launched.add(self.bucket_of_layer[1]); n += self.world > 1
         # dgrad2 also leaves per-32-row column sums of dh1 (592 x 512 instead of 18944 x 512 to sum for db1)
-        ops.linear_dgrad(self.dh2, self.W[1], mask_src=self.h1, mask_scale=inv_keep, out=self.dh1, precision=prec,
+        ops.linear_dgrad(self.dh2, self.W[1], mask_bits=self.h1_bits, mask_scale=inv_keep, out=self.dh1, precision=prec,
                          colsum_partial=self.dh1_colsum, stream=s); n += 1
         # layer 1 (its input needs no gradient); with folded input dW1 = s*(dh1^T raw) + t*db1 1^T
         ops.colsum(self.dh1_colsum, out=self.db[0], stream=s); n += 1

@@ -232,3 +232,27 @@ def test_output_stays_inside_its_rows(M, N):
     ops.linear_wgrad(dy, x, N_out=M, out=arena[:M])
     assert bool((arena[M:] == 5.0).all())
     assert (arena[:M].double() - dy[:, :M].double().T @ x.double()).abs().max().item() < 1e-3
+
+
+@pytest.mark.parametrize("B,N", [(300, 512), (1000, 200), (129, 96)])
+def test_bit_packed_mask_roundtrip(B, N):
+    """A forward GEMM writes (out > 0) as one bit per element; a dgrad consumes those bits instead of the activation and
+    must give exactly what the float mask gives."""
+    ops = _ops()
+    torch.manual_seed(12)
+    K = 96
+    x, w, b = torch.randn(B, K, device="cuda"), torch.randn(N, K, device="cuda") * 0.1, torch.randn(N, device="cuda")
+    words = (N + 31) // 32
+    arena = torch.full((B + 4, words + 1), -1, dtype=torch.int32, device="cuda")
+    bits = arena[:B, :words]
+    h = ops.linear_forward(x, w, b, relu=True, drop_p=0.25, seed=3, mask_bits_out=bits)
+    ref_bits = torch.zeros(B, words * 32, dtype=torch.bool, device="cuda")
+    ref_bits[:, :N] = h > 0
+    weights = (1 << torch.arange(32, device="cuda", dtype=torch.int64))
+    packed = (ref_bits.view(B, words, 32).long() * weights).sum(-1)
+    assert torch.equal(bits.long() & 0xFFFFFFFF, packed)
+    assert bool((arena[B:] == -1).all()) and bool((arena[:, words] == -1).all())
+    dy, w2 = torch.randn(B, 64, device="cuda"), torch.randn(64, N, device="cuda") * 0.1
+    a = ops.linear_dgrad(dy, w2, mask_src=h, mask_scale=4 / 3)
+    c = ops.linear_dgrad(dy, w2, mask_bits=bits, mask_scale=4 / 3)
+    assert torch.equal(a, c)

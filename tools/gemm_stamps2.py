@@ -7,13 +7,16 @@ x = torch.randint(0, 256, (B, 784), device=dev).float(); w1 = torch.randn(512, 7
 h = torch.relu(torch.randn(B, 512, device=dev)); w2 = torch.randn(512, 512, device=dev) * .03
 dy = torch.randn(B, 512, device=dev); out = torch.empty(B, 512, device=dev)
 buf = torch.zeros(512 * 16, dtype=torch.int64, device=dev)
+part = torch.zeros(4 * 148, 512, device=dev)
 cases = {"fwd1": lambda: ops.gemm(x, w1, out, bias=b1, relu=True, drop_p=0.25, seed=1),
          "fwd1_exact": lambda: ops.gemm(x, w1, out, bias=b1, relu=True, drop_p=0.25, seed=1, a_exact=True),
          "fwd1_exact_nodrop": lambda: ops.gemm(x, w1, out, bias=b1, relu=True, a_exact=True),
          "fwd2": lambda: ops.gemm(h, w2, out, bias=b1, relu=True, drop_p=0.25, seed=1),
          "fwd2_bn128": lambda: ops.gemm(h, w2, out, bias=b1, relu=True, drop_p=0.25, seed=1, bn=128),
          "fwd2_bn64": lambda: ops.gemm(h, w2, out, bias=b1, relu=True, drop_p=0.25, seed=1, bn=64),
-         "dgrad2": lambda: ops.linear_dgrad(dy, w2, mask_src=h, mask_scale=4 / 3, out=out)}
+         "dgrad2": lambda: ops.linear_dgrad(dy, w2, mask_src=h, mask_scale=4 / 3, out=out),
+         "dgrad2_colsum": lambda: ops.linear_dgrad(dy, w2, mask_src=h, mask_scale=4 / 3, out=out, colsum_partial=part),
+         "dgrad2_nomask": lambda: ops.linear_dgrad(dy, w2, out=out)}
 for case in (sys.argv[1:] or list(cases)):
     os.environ.pop("RTDC_GEMM_DEBUG_BUF", None)
     for _ in range(3): cases[case]()
