@@ -369,7 +369,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __shared__ uint32_t tmem_base_slot;
   __shared__ __align__(16) float s_bias[MAX_BN];
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);   // warp-uniform for the compiler
   const int lane = threadIdx.x & 31;
 
   // 1024-byte aligned stage ring (swizzle atoms are up to 1024 B), epilogue staging right behind it
@@ -404,7 +404,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
-  const uint32_t tmem_base = tmem_base_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_slot, 0);
   long long* stamps = p.dbg_times ? p.dbg_times + static_cast<size_t>(blockIdx.x) * 8 : nullptr;
   if (stamps && threadIdx.x == 0) { stamps[0] = clock64(); stamps[7] = static_cast<long long>(global_timer_ns()); }
 
@@ -417,7 +417,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    // (the whole warp walks the loop, one elected lane issues: operands stay in uniform registers)
+    {
       int s = 0;
       uint32_t ph = 0;
       for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
@@ -426,9 +427,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int m0 = (tile % p.m_tiles) * BM, n0 = (tile / p.m_tiles) * p.bn;
         for (int it = 0; it < n_iters; ++it) {
           mbar_wait(&empty_bar[s], ph ^ 1u);
+          __syncwarp();
           uint8_t* sa = ring_ptr + static_cast<size_t>(s) * p.stage_bytes;
           uint8_t* sb = sa + p.a_bytes;
-          if (p.debug & 1) {
+          if (!elect_one()) {
+          } else if (p.debug & 1) {
             mbar_arrive(&full_bar[s]);
           } else {
             mbar_expect_tx(&full_bar[s], p.a_bytes + p.b_bytes);
@@ -449,6 +452,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               for (int b = 0; b < p.bn / 32; ++b) tma_load_2d(sb + b * (128 * BK), &tmB, &full_bar[s], n0 + 32 * b, k0);
             }
           }
+          __syncwarp();
           if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
       }
@@ -456,7 +460,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // (converged warp + elect.sync: no per-MMA R2UR election loop, see the CTA-pair kernel)
+    {
       const bool a_exact = p.a_exact != 0, b_exact = p.b_exact != 0;
       // K-major: 8-row groups (SW128 for 128-byte rows, SW64 for 64-byte rows). MN-major: 32-wide MN blocks
       // one TMA box apart, 4-row K groups 512 B apart (SW128 with 32-byte atoms: the only MN-major layout
@@ -486,9 +491,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int it = 0; it < n_iters; ++it) {
           mbar_wait(NSPLIT == 3 ? &ready_bar[s] : &full_bar[s], ph);
           tcgen05_fence_after();
+          __syncwarp();
           const uint32_t sa = ring + static_cast<uint32_t>(s) * p.stage_bytes;
           const uint32_t sb = sa + p.a_bytes;
-          if (p.debug & 2) {
+          if (!elect_one()) {
+          } else if (p.debug & 2) {
             mbar_arrive(&empty_bar[s]);
           } else {
             const int k_left = p.K - (kb_begin + it) * BK;
@@ -517,11 +524,15 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             tcgen05_commit(&empty_bar[s]);  // smem slot reusable once these MMAs have read it
           }
+          __syncwarp();
           if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
-        if (p.debug & 2) mbar_arrive(&tmem_full_bar[buf]);
-        else tcgen05_commit(&tmem_full_bar[buf]);  // accumulators of this unit complete
-        if (stamps && j == 0) stamps[2] = clock64();
+        if (elect_one()) {
+          if (p.debug & 2) mbar_arrive(&tmem_full_bar[buf]);
+          else tcgen05_commit(&tmem_full_bar[buf]);  // accumulators of this unit complete
+          if (stamps && j == 0) stamps[2] = clock64();
+        }
+        __syncwarp();
       }
     }
     __syncwarp();
