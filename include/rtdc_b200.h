@@ -165,6 +165,10 @@ int rtdc_u8_affine_paced(const uint8_t* src, float* dst, size_t n, float scale, 
  */
 typedef struct rtdc_sgd_hyper { float lr, momentum, dampening, weight_decay, grad_scale; int nesterov; int first_step; int pad; } rtdc_sgd_hyper;
 int rtdc_sgd_step(float* p, const float* g, float* m, size_t n, const rtdc_sgd_hyper* hyper_dev, void* stream);
+/* Same, and the block that finishes last also does what rtdc_counter_advance does (first_step = 0, step_counter[0] += 1):
+ * one launch less per training step. hyper_dev->pad is the arrival counter: keep it 0 between calls. */
+int rtdc_sgd_step_advance(float* p, const float* g, float* m, size_t n, rtdc_sgd_hyper* hyper_dev, uint32_t* step_counter_or_null,
+                          void* stream);
 /* Adam / AdamW (decoupled != 0): step counter lives in hyper_dev->step and is advanced by rtdc_adam_advance. */
 typedef struct rtdc_adam_hyper { float lr, beta1, beta2, eps, weight_decay, grad_scale; int decoupled; int step; } rtdc_adam_hyper;
 int rtdc_adam_step(float* p, const float* g, float* m, float* v, size_t n, const rtdc_adam_hyper* hyper_dev, void* stream);

@@ -309,7 +309,7 @@ u8_normalize_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst, si
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, size_t n,
-           const rtdc_sgd_hyper* __restrict__ hp) {
+           rtdc_sgd_hyper* hp, uint32_t* step_counter, int advance) {
   const rtdc_sgd_hyper h = *hp;
   const size_t nvec = n / 4;
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
@@ -340,6 +340,21 @@ sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict
         gr = h.nesterov ? gr + h.momentum * mi : mi;
       }
       p[i] -= h.lr * gr;
+    }
+  }
+  if (advance) {
+    // the block that finishes last clears first_step and bumps the dropout step counter (what a separate one-thread kernel
+    // used to do): every block has read its copy of the hyper-parameters by then
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      const int ticket = atomicAdd(&hp->pad, 1);
+      if (ticket == static_cast<int>(gridDim.x) - 1) {
+        hp->first_step = 0;
+        hp->pad = 0;
+        if (step_counter != nullptr) step_counter[0] += 1u;
+        __threadfence();
+      }
     }
   }
 }
@@ -587,14 +602,23 @@ RTDC_API int rtdc_fold_input_bias(const float* w, int ldw, int rows, int cols, c
   return RTDC_OK;
 }
 
-RTDC_API int rtdc_sgd_step(float* p, const float* g, float* m, size_t n, const rtdc_sgd_hyper* hyper_dev, void* stream) {
+static int sgd_launch(float* p, const float* g, float* m, size_t n, rtdc_sgd_hyper* hyper_dev, uint32_t* counter, int advance, void* stream) {
   if (!p || !g || !hyper_dev) return fail(RTDC_ERR_ARG, "sgd_step: null pointer");
   if (n == 0) return RTDC_OK;
   if ((reinterpret_cast<uintptr_t>(p) & 15u) || (reinterpret_cast<uintptr_t>(g) & 15u) || (reinterpret_cast<uintptr_t>(m) & 15u))
     return fail(RTDC_ERR_ARG, "sgd_step: arenas must be 16-byte aligned");
-  sgd_kernel<<<grid_for(n / 4 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, n, hyper_dev);
+  sgd_kernel<<<grid_for(n / 4 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, n, hyper_dev, counter, advance);
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;
+}
+
+RTDC_API int rtdc_sgd_step(float* p, const float* g, float* m, size_t n, const rtdc_sgd_hyper* hyper_dev, void* stream) {
+  return sgd_launch(p, g, m, n, const_cast<rtdc_sgd_hyper*>(hyper_dev), nullptr, 0, stream);
+}
+
+RTDC_API int rtdc_sgd_step_advance(float* p, const float* g, float* m, size_t n, rtdc_sgd_hyper* hyper_dev, uint32_t* step_counter_or_null,
+                                   void* stream) {
+  return sgd_launch(p, g, m, n, hyper_dev, step_counter_or_null, 1, stream);
 }
 
 RTDC_API int rtdc_adam_step(float* p, const float* g, float* m, float* v, size_t n, const rtdc_adam_hyper* hyper_dev, void* stream) {

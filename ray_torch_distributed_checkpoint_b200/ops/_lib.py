@@ -82,6 +82,8 @@ def _declare(lib):
     lib.rtdc_u8_affine_paced.restype = i
     lib.rtdc_fold_input_bias.argtypes = [vp, i, i, i, vp, f, vp, vp]
     lib.rtdc_sgd_step.argtypes = [vp, vp, vp, sz, vp, vp]
+    lib.rtdc_sgd_step_advance.argtypes = [vp, vp, vp, sz, vp, vp, vp]
+    lib.rtdc_sgd_step_advance.restype = i
     lib.rtdc_adam_step.argtypes = [vp, vp, vp, vp, sz, vp, vp]
     lib.rtdc_adam_advance.argtypes = [vp, vp]
     lib.rtdc_counter_advance.argtypes = [vp, vp, vp]

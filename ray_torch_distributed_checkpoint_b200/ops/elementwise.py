@@ -146,13 +146,21 @@ class SgdState:
         self.dev.copy_(torch.frombuffer(bytearray(bytes(self.host)), dtype=torch.uint8), non_blocking=False)
 
 
-def sgd_step(p: torch.Tensor, g: torch.Tensor, m: Optional[torch.Tensor], state: SgdState, stream=None):
-    """One fused SGD(+momentum) step over flat fp32 arenas (in place on ``p`` and ``m``)."""
+def sgd_step(p: torch.Tensor, g: torch.Tensor, m: Optional[torch.Tensor], state: SgdState, stream=None, *,
+             advance: bool = False, counter: Optional[torch.Tensor] = None):
+    """One fused SGD(+momentum) step over flat fp32 arenas (in place on ``p`` and ``m``). ``advance``: the kernel also
+    clears ``first_step`` and adds 1 to ``counter`` (what :func:`counter_advance` does in its own launch)."""
     n = p.numel()
     if g.numel() != n or (m is not None and m.numel() != n):
         raise ValueError("arena sizes differ")
-    _lib.check(_lib.load().rtdc_sgd_step(p.data_ptr(), g.data_ptr(), m.data_ptr() if m is not None else p.data_ptr(), n,
-                                         state.dev.data_ptr(), _lib.stream_ptr(stream)))
+    lib = _lib.load()
+    mp = m.data_ptr() if m is not None else p.data_ptr()
+    if advance:
+        _lib.check(lib.rtdc_sgd_step_advance(p.data_ptr(), g.data_ptr(), mp, n, state.dev.data_ptr(),
+                                             counter.data_ptr() if counter is not None else None, _lib.stream_ptr(stream)))
+        state.host.first_step = 0
+    else:
+        _lib.check(lib.rtdc_sgd_step(p.data_ptr(), g.data_ptr(), mp, n, state.dev.data_ptr(), _lib.stream_ptr(stream)))
 
 
 def counter_advance(counter: Optional[torch.Tensor], sgd_state: Optional[SgdState] = None, stream=None):

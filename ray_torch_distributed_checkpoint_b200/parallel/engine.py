@@ -251,8 +251,7 @@ class MLPTrainEngine:
             self.symm.all_reduce(self.g_off, self.total, scale=1.0 / self.world, algo=self.algo, stream=s)
         elif self.world > 1:
             s.wait_stream(self.comm_stream)
-        ops.sgd_step(self.p_arena, self.g_arena, self.m_arena, self.sgd, stream=s); n += 1
-        ops.counter_advance(self.step_counter, self.sgd, stream=s); n += 1
+        ops.sgd_step(self.p_arena, self.g_arena, self.m_arena, self.sgd, stream=s, advance=True, counter=self.step_counter); n += 1
         return n
 
     def _enqueue_eval(self, s: torch.cuda.Stream, from_u8: bool, slot: int) -> int:

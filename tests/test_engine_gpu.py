@@ -62,7 +62,7 @@ def test_engine_matches_reference_training(use_graph, fused_head):
         assert diff.norm() / ref.norm() < 2e-2, (i, float(diff.norm() / ref.norm()))
     if use_graph:
         assert ("train_f32", 0) in eng._graphs and ("train_f32", 1) in eng._graphs
-    assert eng.kernel_launches_per_step["train_f32"] >= 12
+    assert eng.kernel_launches_per_step["train_f32"] >= 10
     eng.close()
 
 
