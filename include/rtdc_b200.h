@@ -119,6 +119,12 @@ int rtdc_mlp_head_train(const float* h, int ldh, const float* w, const float* bi
                         int K, int classes, float grad_scale, float mask_scale, float* dh, int lddh, float* dw,
                         float* db, float* loss, float* db_below /* [K] column sums of dh, or NULL */,
                         void* scratch, size_t scratch_bytes, void* stream);
+/* The same in two launches: part 1 = the pass over h (dh is final, dw/db/loss/db_below are still per-block partials in
+ * scratch), part 2 = the reduction of those partials (same arguments, same scratch, ordered after part 1); part 0 = both.
+ * A caller can run part 2 on a side stream next to the kernels that only need dh. */
+int rtdc_mlp_head_train_part(const float* h, int ldh, const float* w, const float* bias, const int64_t* labels, int rows,
+                             int K, int classes, float grad_scale, float mask_scale, float* dh, int lddh, float* dw,
+                             float* db, float* loss, float* db_below, void* scratch, size_t scratch_bytes, void* stream, int part);
 
 /* ------------------------------------------------------------------------------------------
  * Column sums of a [rows, cols] fp32 matrix (bias gradients, K6): out[c] = sum_r x[r*ld + c].

@@ -323,9 +323,11 @@ RTDC_API size_t rtdc_mlp_head_scratch_bytes(int rows, int K, int classes) {
   return g * (static_cast<size_t>(classes) * K + K + 16 + 4) * sizeof(float) + 256;
 }
 
-RTDC_API int rtdc_mlp_head_train(const float* h, int ldh, const float* w, const float* bias, const int64_t* labels, int rows,
-                                 int K, int classes, float grad_scale, float mask_scale, float* dh, int lddh, float* dw,
-                                 float* db, float* loss, float* db_below, void* scratch, size_t scratch_bytes, void* stream) {
+// part: 0 = both kernels on `stream`; 1 = the pass over h only (per-block partials stay in scratch); 2 = the reduction of
+// those partials only. 1 and 2 let a caller put the small reduction on a side stream, next to whatever follows the head.
+static int head_train_impl(const float* h, int ldh, const float* w, const float* bias, const int64_t* labels, int rows,
+                           int K, int classes, float grad_scale, float mask_scale, float* dh, int lddh, float* dw,
+                           float* db, float* loss, float* db_below, void* scratch, size_t scratch_bytes, void* stream, int part) {
   if (!h || !w || !labels || !dh || !dw || !db || !loss) return fail(RTDC_ERR_ARG, "mlp_head_train: null pointer");
   if (rows <= 0 || K <= 0 || K > HD_MAXK || (K & 3) || (ldh & 3) || (lddh & 3))
     return fail(RTDC_ERR_LIMIT, "mlp_head_train: hidden width must be a multiple of 4 and <= %d, row pitches multiples of 4 (K=%d)", HD_MAXK, K);
@@ -345,18 +347,38 @@ RTDC_API int rtdc_mlp_head_train(const float* h, int ldh, const float* w, const 
   p.dbh_partial = db_below ? p.loss_partial + ((grid + 3) & ~3) : nullptr;
   const size_t smem = head_smem_bytes(classes, K);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (classes == 10) {
-    RTDC_CUDA_CHECK(cudaFuncSetAttribute(mlp_head_train_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    mlp_head_train_kernel<10><<<grid, HD_THREADS, smem, st>>>(p);
-  } else {
-    RTDC_CUDA_CHECK(cudaFuncSetAttribute(mlp_head_train_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    mlp_head_train_kernel<16><<<grid, HD_THREADS, smem, st>>>(p);
+  if (part != 2) {
+    if (classes == 10) {
+      RTDC_CUDA_CHECK(cudaFuncSetAttribute(mlp_head_train_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+      mlp_head_train_kernel<10><<<grid, HD_THREADS, smem, st>>>(p);
+    } else {
+      RTDC_CUDA_CHECK(cudaFuncSetAttribute(mlp_head_train_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+      mlp_head_train_kernel<16><<<grid, HD_THREADS, smem, st>>>(p);
+    }
+    RTDC_CUDA_CHECK(cudaGetLastError());
   }
-  RTDC_CUDA_CHECK(cudaGetLastError());
-  const int CK = classes * K;
-  const int total = CK + (db_below ? K : 0);
-  mlp_head_reduce_kernel<<<(total + 31) / 32, 256, 0, st>>>(p.dw_partial, p.db_partial, p.loss_partial, grid, CK, classes, rows, dw, db, loss,
-                                                          p.dbh_partial, K, db_below);
-  RTDC_CUDA_CHECK(cudaGetLastError());
+  if (part != 1) {
+    const int CK = classes * K;
+    const int total = CK + (db_below ? K : 0);
+    mlp_head_reduce_kernel<<<(total + 31) / 32, 256, 0, st>>>(p.dw_partial, p.db_partial, p.loss_partial, grid, CK, classes, rows, dw, db, loss,
+                                                            p.dbh_partial, K, db_below);
+    RTDC_CUDA_CHECK(cudaGetLastError());
+  }
   return RTDC_OK;
+}
+
+RTDC_API int rtdc_mlp_head_train(const float* h, int ldh, const float* w, const float* bias, const int64_t* labels, int rows,
+                                 int K, int classes, float grad_scale, float mask_scale, float* dh, int lddh, float* dw,
+                                 float* db, float* loss, float* db_below, void* scratch, size_t scratch_bytes, void* stream) {
+  return head_train_impl(h, ldh, w, bias, labels, rows, K, classes, grad_scale, mask_scale, dh, lddh, dw, db, loss, db_below, scratch,
+                         scratch_bytes, stream, 0);
+}
+
+RTDC_API int rtdc_mlp_head_train_part(const float* h, int ldh, const float* w, const float* bias, const int64_t* labels, int rows,
+                                      int K, int classes, float grad_scale, float mask_scale, float* dh, int lddh, float* dw,
+                                      float* db, float* loss, float* db_below, void* scratch, size_t scratch_bytes, void* stream,
+                                      int part) {
+  if (part < 0 || part > 2) return fail(RTDC_ERR_ARG, "mlp_head_train_part: part must be 0, 1 or 2");
+  return head_train_impl(h, ldh, w, bias, labels, rows, K, classes, grad_scale, mask_scale, dh, lddh, dw, db, loss, db_below, scratch,
+                         scratch_bytes, stream, part);
 }

@@ -73,6 +73,8 @@ def _declare(lib):
     lib.rtdc_mlp_head_scratch_bytes.restype = sz
     lib.rtdc_mlp_head_train.argtypes = [vp, i, vp, vp, vp, i, i, i, f, f, vp, i, vp, vp, vp, vp, vp, sz, vp]
     lib.rtdc_mlp_head_train.restype = i
+    lib.rtdc_mlp_head_train_part.argtypes = [vp, i, vp, vp, vp, i, i, i, f, f, vp, i, vp, vp, vp, vp, vp, sz, vp, i]
+    lib.rtdc_mlp_head_train_part.restype = i
     lib.rtdc_colsum_scratch_bytes.argtypes = [i, i]
     lib.rtdc_colsum_scratch_bytes.restype = sz
     lib.rtdc_colsum.argtypes = [vp, i, i, i, vp, vp, sz, vp]

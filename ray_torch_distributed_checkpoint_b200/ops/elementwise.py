@@ -53,23 +53,26 @@ def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor, *, classes
 def mlp_head_train(h: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], labels: torch.Tensor, *,
                    dh: torch.Tensor, dw: torch.Tensor, db: torch.Tensor, loss: Optional[torch.Tensor] = None,
                    grad_scale: Optional[float] = None, mask_scale: float = 1.0, db_below: Optional[torch.Tensor] = None,
-                   stream=None) -> torch.Tensor:
+                   stream=None, part: int = 0, scratch_stream=None) -> torch.Tensor:
     """Fused last layer for training: ``z = relu(h @ weight.T + bias)``, mean cross-entropy, and the layer's
     backward (``dw``, ``db``, ``dh = (dz @ weight) * (h > 0) * mask_scale``) in one pass over ``h``.
     ``weight`` is ``[classes, K]`` with 10 or 16 classes and ``K <= 512``. ``db_below[K]`` optionally receives the
-    column sums of ``dh`` (the bias gradient of the layer that produced ``h``)."""
+    column sums of ``dh`` (the bias gradient of the layer that produced ``h``). ``part`` 1 / 2 run only the pass over
+    ``h`` / only the reduction of its per-block partials (same arguments; ``scratch_stream`` names the stream whose scratch
+    buffer both calls share when the reduction goes to a side stream)."""
     rows, K = h.shape
     classes = weight.shape[0]
     if loss is None:
         loss = torch.empty((), dtype=torch.float32, device=h.device)
     lib = _lib.load()
-    ws = scratch_for("head", lib.rtdc_mlp_head_scratch_bytes(rows, K, classes), h.device, stream)
+    ws = scratch_for("head", lib.rtdc_mlp_head_scratch_bytes(rows, K, classes), h.device,
+                     scratch_stream if scratch_stream is not None else stream)
     gs = (1.0 / rows) if grad_scale is None else grad_scale
-    _lib.check(lib.rtdc_mlp_head_train(h.data_ptr(), h.stride(0), weight.data_ptr(), bias.data_ptr() if bias is not None else None,
-                                       labels.data_ptr(), rows, K, classes, gs, mask_scale, dh.data_ptr(), dh.stride(0),
-                                       dw.data_ptr(), db.data_ptr(), loss.data_ptr(),
-                                       db_below.data_ptr() if db_below is not None else None, ws.data_ptr(), ws.numel(),
-                                       _lib.stream_ptr(stream)))
+    _lib.check(lib.rtdc_mlp_head_train_part(h.data_ptr(), h.stride(0), weight.data_ptr(), bias.data_ptr() if bias is not None else None,
+                                            labels.data_ptr(), rows, K, classes, gs, mask_scale, dh.data_ptr(), dh.stride(0),
+                                            dw.data_ptr(), db.data_ptr(), loss.data_ptr(),
+                                            db_below.data_ptr() if db_below is not None else None, ws.data_ptr(), ws.numel(),
+                                            _lib.stream_ptr(stream), part))
     return loss
 
 

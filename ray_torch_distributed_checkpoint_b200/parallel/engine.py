@@ -81,6 +81,7 @@ class MLPTrainEngine:
         # the GEMMs, one latency instead of two). ar_overlap_blocks caps the grid of an overlapped bucket reduction.
         self.ar_mode = ar_mode or _os.environ.get("RTDC_AR_MODE", "merged")
         self.ar_overlap_blocks = int(_os.environ.get("RTDC_AR_OVERLAP_BLOCKS", "0")) if ar_overlap_blocks is None else ar_overlap_blocks
+        self.side_small = _os.environ.get("RTDC_SIDE_SMALL", "1") != "0"
 
         # ---- arenas (bucket order == torch DDP's for this model)
         named = [(n, p) for n, p in model.named_parameters()]
@@ -120,6 +121,9 @@ class MLPTrainEngine:
         self.x = [torch.zeros(B, self.d_in, device=dev) for _ in range(2)]
         self.y = [torch.zeros(B, dtype=torch.int64, device=dev) for _ in range(2)]
         self.stage_stream = torch.cuda.Stream(dev)
+        # small reductions (head partials, db1) run on a side stream next to the wgrad GEMMs, whose 144 CTAs leave four SMs
+        # idle; only with one merged all-reduce (a bucketed reduction would need their results earlier)
+        self.aux_stream = torch.cuda.Stream(dev)
         import os as _os
         self.stage_blocks = int(_os.environ.get("RTDC_STAGE_BLOCKS", "0"))   # optional grid cap of an overlapped conversion (0 = full speed: measured best)
         self._ready: List[Optional[torch.cuda.Event]] = [None, None]   # slot staged
@@ -213,12 +217,21 @@ class MLPTrainEngine:
         B, prec = self.B, self.precision
         inv_keep = 1.0 / (1.0 - self.p_drop) if self.p_drop > 0 else 1.0
         fused_head = self.fused_head
+        side = self.side_small and (self.world == 1 or self.ar_mode == "merged")
+        aux = self.aux_stream
         n = self._forward(s, True, from_u8, slot, with_logits=not fused_head)
         x, y = self.x[slot], self.y[slot]
         if fused_head:
-            # layer 3 forward + loss + layer 3 backward in one pass over h2 (exact fp32 on the CUDA cores)
-            ops.mlp_head_train(self.h2, self.W[2], self.b[2], y, dh=self.dh2, dw=self.dW[2], db=self.db[2], loss=self.loss,
-                               grad_scale=1.0 / B, mask_scale=inv_keep, db_below=self.db[1], stream=s); n += 2   # also emits db2
+            # layer 3 forward + loss + layer 3 backward in one pass over h2 (exact fp32 on the CUDA cores); also emits db2
+            hk = dict(dh=self.dh2, dw=self.dW[2], db=self.db[2], loss=self.loss, grad_scale=1.0 / B, mask_scale=inv_keep,
+                      db_below=self.db[1])
+            if side:
+                ops.mlp_head_train(self.h2, self.W[2], self.b[2], y, stream=s, part=1, **hk)
+                aux.wait_stream(s)                                   # the partials' reduction overlaps wgrad2
+                ops.mlp_head_train(self.h2, self.W[2], self.b[2], y, stream=aux, part=2, scratch_stream=s, **hk)
+            else:
+                ops.mlp_head_train(self.h2, self.W[2], self.b[2], y, stream=s, **hk)
+            n += 2
         else:
             ops.softmax_cross_entropy(self.z, y, classes=self.d_out, dlogits=self.dz, grad_scale=1.0 / B, relu_mask=True,
                                       loss_out=self.loss, dbias_out=self.db[2], stream=s); n += 1   # also emits db3
@@ -236,7 +249,12 @@ class MLPTrainEngine:
         ops.linear_dgrad(self.dh2, self.W[1], mask_bits=self.h1_bits, mask_scale=inv_keep, out=self.dh1, precision=prec,
                          colsum_partial=self.dh1_colsum, stream=s); n += 1
         # layer 1 (its input needs no gradient); with folded input dW1 = s*(dh1^T raw) + t*db1 1^T
-        ops.colsum(self.dh1_colsum, out=self.db[0], stream=s); n += 1
+        side_cs = side and not (from_u8 and self.input_mode == "fold")     # the folded wgrad1 epilogue reads db1
+        if side_cs:
+            aux.wait_stream(s)
+            ops.colsum(self.dh1_colsum, out=self.db[0], stream=aux); n += 1      # overlaps wgrad1
+        else:
+            ops.colsum(self.dh1_colsum, out=self.db[0], stream=s); n += 1
         if from_u8 and self.input_mode == "shift":
             ops.linear_wgrad(self.dh1, x, out=self.dW[0], precision=prec, x_exact=True, alpha=self.in_scale, stream=s); n += 2
         elif from_u8 and self.input_mode == "fold":
@@ -247,6 +265,8 @@ class MLPTrainEngine:
         for b in range(len(self.buckets)):
             if b not in launched:
                 self._reduce_bucket(b, s, last=True); n += self.world > 1
+        if side:
+            s.wait_stream(aux)
         if self.world > 1 and self.ar_mode == "merged":
             self.symm.all_reduce(self.g_off, self.total, scale=1.0 / self.world, algo=self.algo, stream=s)
         elif self.world > 1:
