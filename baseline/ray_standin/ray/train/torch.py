@@ -50,6 +50,15 @@ class _DeviceLoader:
                 if cuda:
                     ev.record()
                 rec.append(("step_begin", time.perf_counter(), ev))
+                if cuda and _dist.is_initialized() and _dist.get_world_size() > 1:
+                    # second begin stamp once EVERY rank holds its batch: without it a step's device interval at N >= 2
+                    # also holds the slowest peer's CPU-loader stall (it surfaces inside the NCCL all-reduce)
+                    _dist.barrier()
+                    ev2 = _torch.cuda.Event(enable_timing=True)
+                    ev2.record()
+                    rec.append(("step_begin_synced", time.perf_counter(), ev2))
+                else:
+                    rec.append(("step_begin_synced", time.perf_counter(), ev))
             yield moved
             if rec is not None:
                 ev = _torch.cuda.Event(enable_timing=True) if cuda else None

@@ -10,13 +10,23 @@ momentum 0.9, dropout 0.25, DDP) at N B200 GPUs, max over ranks — BASELINE.jso
 
 Weak scaling: the per-GPU batch is fixed (--batch-per-gpu), the global batch is N times that.
 
-Two numbers per run:
-* ``value``: K optimizer steps timed on the device with CUDA events (barrier + synchronize on both
-  sides, max over ranks); inputs rotate over several device-resident batches so that each step's
-  working set (> 126 MB L2) streams from HBM.
-* ``e2e.value``: the same K steps driven through the public API a user calls — ``data.U8BatchLoader``
-  (pinned host dataset -> per-step H2D of that step's uint8 pixels + int64 labels) feeding
-  ``parallel.MLPTrainEngine.step`` — with the step's loss read back to the host every step.
+Arms (``--impl``):
+
+* ``ours`` (default): ``examples/my_module.train_fashion_mnist(...)`` — the reference's program written against this
+  framework — through ``TorchTrainer.fit()``: worker launch (native launcher at N = 1, the enclosing torchrun ranks at
+  N > 1), ``prepare_data_loader`` (uint8 dataset in pinned host memory, per-step H2D of that step's pixels + labels),
+  ``prepare_model`` (engine-backed: the literal ``model(X) / loss_fn / backward / optimizer.step()`` loop replays one
+  CUDA graph per step), per-epoch validation, asynchronous checkpoint and ``report``. Timed exactly like the reference
+  arm: CUDA events at the training loader's batch boundaries.
+* ``ours-engine``: ``parallel.MLPTrainEngine`` driven by hand (no trainer, loader optional) — the kernel-path number.
+* ``reference``: the unmodified reference (``baseline/_ref``) on stock torch DDP + NCCL + cuBLAS.
+
+Numbers per run (R back-to-back blocks of K steps; median block, min/max alongside):
+* ``value``: sum over a block's K steps of the device interval [batch handed to the loop, loop back for the next batch]
+  (loader stalls, validation and checkpointing excluded), max over ranks.
+* ``e2e.value``: device time from the end of the previous block's last step to the end of this block's last step —
+  everything in between included: the previous epoch's validation, checkpoint snapshot and report, the epoch's
+  shuffle, every step's H2D copy, and the per-step loss written back to pinned host memory.
 """
 from __future__ import annotations
 
@@ -108,8 +118,127 @@ def _max_over_ranks(value: float, device) -> float:
     return float(t.item())
 
 
-# ------------------------------------------------------------------------------------------------ our arm
+L2_POLICY = ("inputs larger than L2, no explicit flush: every step consumes a fresh batch from host memory (14.9 MB of uint8 "
+             "pixels ours / 59 MB of fp32 reference) and streams > 200 MB of activations through HBM (L2 is 126 MB)")
+
+
+def _config(global_batch: int, per_gpu: int, world: int):
+    """Identical for every arm (arm-specific facts go to the sibling key "arm")."""
+    return {"model": MODEL, "global_batch": global_batch, "batch_per_gpu": per_gpu, "seq_len": None,
+            "parallelism": f"dp{world}", "l2_policy": L2_POLICY}
+
+
+def _write_dataset(home: str, n_train: int, n_test: int, rank: int):
+    """Synthetic idx files where torchvision.datasets.FashionMNIST looks for them (~/data); rank 0 writes, others wait."""
+    os.makedirs(home, exist_ok=True)
+    marker = os.path.join(home, f"data_ready_{n_train}_{n_test}")
+    if rank == 0 and not os.path.exists(marker):
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        import make_idx
+        make_idx.write(os.path.join(home, "data"), n_train=n_train, n_test=n_test)
+        open(marker, "w").close()
+    t_wait = time.time()
+    while not os.path.exists(marker):
+        time.sleep(0.2)
+        if time.time() - t_wait > 600:
+            raise SystemExit("timed out waiting for the synthetic dataset")
+
+
+def _median_block(blocks):
+    return statistics.median(blocks), min(blocks), max(blocks)
+
+
+# ------------------------------------------------------------------------------------------------ our arm, public API
 def run_ours(args):
+    import glob
+    import torch
+    import torch.distributed as dist
+
+    rank, world, local = _dist_env()
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}; launch with torch.distributed.run --nproc-per-node {args.gpus}")
+    B, K, W, R = args.batch_per_gpu, args.steps, max(args.warmup, 3), max(1, args.repeats)
+    S = K                                         # steps per epoch: every timed block is one epoch
+    warm_epochs = -(-W // S)
+    epochs = warm_epochs + R
+    home = os.path.join(ROOT, ".bench_home")      # scratch inside the repo copy, ignored by git and gpurun
+    os.environ["HOME"] = home
+    _write_dataset(home, n_train=B * world * S, n_test=args.val_size, rank=rank)
+    timing_path = os.path.join(home, f"timing_{os.getpid() if world == 1 else os.environ.get('MASTER_PORT', '0')}")
+    for f in glob.glob(timing_path + ".*"):
+        if rank == 0:
+            os.unlink(f)
+    os.environ["RTDC_STEP_TIMING"] = timing_path
+    os.environ.pop("RTDC_SYNTHETIC_DATA", None)
+    if world > 1:
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))   # control plane of the trainer + this script
+        dist.barrier()
+    sys.path.insert(0, os.path.join(ROOT, "examples"))
+    import my_module
+    storage = os.path.join(home, "storage")
+    wall0 = time.perf_counter()
+    with ClockSampler(local) as clk:
+        result = my_module.train_fashion_mnist(num_workers=world, use_gpu=True, global_batch_size=B * world, learning_rate=1e-3,
+                                               epochs=epochs, checkpoint_storage_path=storage)
+    wall = time.perf_counter() - wall0
+    if world > 1:
+        dist.barrier()
+    out = None
+    if rank == 0:
+        per_rank = []
+        for r in range(world):
+            with open(f"{timing_path}.{r}") as f:
+                per_rank.append(json.load(f))
+        n = min(t["steps"] for t in per_rank)
+        if n < (warm_epochs + R) * S:
+            raise SystemExit(f"expected {(warm_epochs + R) * S} timed steps, the loader recorded {n}")
+        dev_blocks, e2e_blocks = [], []
+        for r in range(R):
+            lo, hi = (warm_epochs + r) * S, (warm_epochs + r + 1) * S
+            dev_blocks.append(max(sum(t["device_ms"][lo:hi]) for t in per_rank))
+            e2e_blocks.append(max(t["end_ms_since_first_begin"][hi - 1] - t["end_ms_since_first_begin"][lo - 1] for t in per_rank))
+        ms, ms_min, ms_max = _median_block(dev_blocks)
+        e2e_ms, e2e_min, e2e_max = _median_block(e2e_blocks)
+        extra = per_rank[0].get("extra", {})
+        lps = int(extra.get("launches_per_train_step", 0))
+        gb = B * world
+        flops = 3209216 * gb * K
+        out = {
+            "metric": METRIC, "value": round(gb * K / (ms / 1e3), 1), "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "fp32 (3xTF32 split on tcgen05 tensor cores, fp32 accumulate in TMEM; matches the reference's fp32)",
+            "data": "synthetic FashionMNIST-shape idx files (uint8 28x28 images, labels 0..9) read by torchvision.datasets.FashionMNIST, random-init weights",
+            "impl": "ours",
+            "config": _config(gb, B, world),
+            "arm": {"entry": "examples/my_module.py::train_fashion_mnist -> TorchTrainer.fit() -> train_func_per_worker (prepare_data_loader, "
+                             "prepare_model = engine-backed, nn.CrossEntropyLoss, optim.SGD, per-epoch validation + async checkpoint + report)",
+                    "launcher": "rtdc-launch worker group (driver mode)" if world == 1 else "enclosing torch.distributed.run ranks (SPMD mode)",
+                    "epochs": epochs, "steps_per_epoch": S, "val_samples": args.val_size, "cuda_graph": True,
+                    "gradient_path": extra.get("gradient_path"), "host": {"cpu_count": os.cpu_count()}},
+            "clocks": clk.summary(),
+            "repeats": R,
+            "ms_per_step_min": round(ms_min / K, 4), "ms_per_step_max": round(ms_max / K, 4),
+            "e2e": {"value": round(gb * K / (e2e_ms / 1e3), 1), "unit": "samples/s", "ms_per_step": round(e2e_ms / K, 4),
+                    "ms_per_step_min": round(e2e_min / K, 4), "ms_per_step_max": round(e2e_max / K, 4),
+                    "h2d_bytes_per_step": int(extra.get("h2d_bytes_per_step", B * 785)), "d2h_bytes_per_step": 4,
+                    "window": "end of the previous epoch's last step -> end of this epoch's last step: validation, checkpoint "
+                              "snapshot, report, epoch shuffle, per-step H2D and loss write-back included",
+                    "api": "my_module.train_fashion_mnist (torchvision dataset -> prepare_data_loader -> U8BatchLoader H2D -> EngineModel step)"},
+            "gpu_launches": lps * K,
+            "gpu_launches_per_step": lps,
+            "tflops_fp32_equiv": round(flops / (ms / 1e3) / 1e12, 2),
+            "fit_wall_s": round(wall, 2),
+            "final_metrics": {k: v for k, v in (getattr(result, "metrics", None) or {}).items() if not str(k).startswith("_")},
+        }
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------ our arm, engine by hand
+def run_ours_engine(args):
     import torch
     import torch.distributed as dist
     from ray_torch_distributed_checkpoint_b200 import data, ops
@@ -126,9 +255,10 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)      # control plane + max-over-ranks only
     ops.load_library()
-    B, K, W = args.batch_per_gpu, args.steps, args.warmup
+    B, K, W, R = args.batch_per_gpu, args.steps, max(args.warmup, 3), max(1, args.repeats)
     torch.manual_seed(1234)
-    eng = MLPTrainEngine(NeuralNetwork(), batch_size=B, lr=1e-3, momentum=0.9, device=dev, seed=2026, algo=args.algo)
+    eng = MLPTrainEngine(NeuralNetwork(), batch_size=B, lr=1e-3, momentum=0.9, device=dev, seed=2026, algo=args.algo,
+                         ar_mode=args.ar_mode)
 
     # ---- synthetic FashionMNIST-shape data: uint8 pixels, int64 labels
     rot = args.rotate
@@ -142,87 +272,80 @@ def run_ours(args):
         torch.cuda.synchronize(dev)
 
     # ---- device-timed region. Batch i+1 is staged (device copy + uint8 -> fp32 conversion on the engine's staging
-    # stream) before step i is launched, so the conversion overlaps that step; the timed region holds exactly K
-    # stagings and K steps (the first staging is exposed, the others overlap).
-    for i in range(max(W, 3)):
+    # stream) before step i is launched, so the conversion overlaps that step; each block holds exactly K stagings and K steps.
+    for i in range(W):
         eng.step(dev_x[i % rot], dev_y[i % rot])
     barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    blocks = []
     with ClockSampler(local) as clk:
-        barrier()
-        e0.record()
-        eng.stage(dev_x[0], dev_y[0])
-        for i in range(K):
-            if i + 1 < K:
-                eng.stage(dev_x[(i + 1) % rot], dev_y[(i + 1) % rot])
-            eng.step()
-        e1.record()
-        torch.cuda.synchronize(dev)
-        barrier()
-    ms = _max_over_ranks(e0.elapsed_time(e1), dev)
+        for r in range(R):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            e0.record()
+            eng.stage(dev_x[0], dev_y[0])
+            for i in range(K):
+                if i + 1 < K:
+                    eng.stage(dev_x[(i + 1) % rot], dev_y[(i + 1) % rot])
+                eng.step()
+            e1.record()
+            torch.cuda.synchronize(dev)
+            barrier()
+            blocks.append(_max_over_ranks(e0.elapsed_time(e1), dev))
+    ms, ms_min, ms_max = _median_block(blocks)
     launches_per_step = eng.kernel_launches_per_step.get("train_u8", 0)
     final_loss = float(eng.loss.item())
 
-    # ---- end to end through the public API: pinned host dataset -> H2D each step -> step -> loss D2H each step
-    n_host = B * (K + max(W, 3))
+    # ---- end to end with the loader: pinned host dataset -> H2D each step -> step -> loss written to pinned host memory each step
+    n_host = B * (K + W)
     hx = torch.randint(0, 256, (n_host, 784), dtype=torch.uint8, generator=g)
     hy = torch.randint(0, 10, (n_host,), generator=g)
-    loader = data.U8BatchLoader(hx, hy, B, dev, shuffle=True, seed=5, lookahead=args.lookahead,
-                                prefetch_next_epoch=False)   # one epoch only: no background shuffle of a next one
-    loss_host = torch.zeros(4, dtype=torch.float32).pin_memory()
-    it = iter(loader)
-    for _ in range(max(W, 3)):
+    loader = data.U8BatchLoader(hx, hy, B, dev, shuffle=True, seed=5, lookahead=args.lookahead, prefetch_next_epoch=True)
+    e2e_blocks = []
+    for r in range(R + 1):                                    # one epoch per block; the first is warm-up
+        loader.sampler.set_epoch(r)
+        barrier()
+        t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+        wall0 = time.perf_counter()
+        t0.record()
+        it = iter(loader)                                     # joins this epoch's shuffle thread, starts the next epoch's
         xb, yb = next(it)
-        eng.step(xb, yb)
-    barrier()
-    losses = []
-    pending = []                                              # (slot, event) of loss copies in flight
-    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
-    wall0 = time.perf_counter()
-    t0.record()
-    xb, yb = next(it)                                         # step 0's H2D (exposed)
-    eng.stage(xb, yb)
-    for i in range(K):
-        if i + 1 < K:
-            xb, yb = next(it)                                 # next step's H2D (issued `lookahead` steps ahead) ...
-            eng.stage(xb, yb)                                 # ... and conversion, overlapping this step
-        loss = eng.step()
-        slot = i % 4
-        loss_host[slot].copy_(loss, non_blocking=True)        # this step's D2H
-        ev = torch.cuda.Event(); ev.record()
-        pending.append((slot, ev))
-        if len(pending) > 1:                                  # read the previous step's loss while this one runs
-            s_, e_ = pending.pop(0)
-            e_.synchronize()
-            losses.append(float(loss_host[s_]))
-    for s_, e_ in pending:
-        e_.synchronize()
-        losses.append(float(loss_host[s_]))
-    t1.record()
-    torch.cuda.synchronize(dev)
-    wall = time.perf_counter() - wall0
-    barrier()
-    e2e_ms = _max_over_ranks(max(t0.elapsed_time(t1), wall * 1e3), dev)
-    assert len(losses) == K and all(l == l for l in losses)
+        eng.stage(xb, yb)
+        for i in range(K + W):
+            if i + 1 < K + W:
+                xb, yb = next(it)                             # next step's H2D (issued `lookahead` steps ahead) ...
+                eng.stage(xb, yb)                             # ... and conversion, overlapping this step
+            eng.step()
+        t1.record()
+        torch.cuda.synchronize(dev)
+        losses = eng.core.recent_losses(K + W)                # what the kernels wrote to the pinned ring, one per step
+        wall = time.perf_counter() - wall0
+        for _ in it:
+            pass
+        barrier()
+        assert len(losses) == K + W and all(l == l for l in losses)
+        if r > 0:
+            e2e_blocks.append(_max_over_ranks(max(t0.elapsed_time(t1), wall * 1e3), dev) * K / (K + W))
+    e2e_ms, e2e_min, e2e_max = _median_block(e2e_blocks)
 
     global_batch = B * world
-    value = global_batch * K / (ms / 1e3)
-    e2e_value = global_batch * K / (e2e_ms / 1e3)
     flops = 3209216 * global_batch * K
     out = {
-        "metric": METRIC, "value": round(value, 1), "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W,
+        "metric": METRIC, "value": round(global_batch * K / (ms / 1e3), 1), "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "fp32 (3xTF32 split on tcgen05 tensor cores, fp32 accumulate in TMEM; matches the reference's fp32)",
-        "data": "synthetic FashionMNIST-shape uint8 28x28 images + int64 labels, random-init weights",
-        "impl": "ours",
-        "config": {"model": MODEL, "global_batch": global_batch, "batch_per_gpu": B, "seq_len": None,
-                   "parallelism": f"dp{world}", "l2_policy": f"no flush: inputs rotate over {rot} device batches and the "
-                   f"per-step working set (~{int(B * (784 * 5 + 512 * 16 + 128) / 1e6)} MB of activations) exceeds the 126 MB L2",
-                   "allreduce": f"{args.algo}/{eng.ar_mode}", "cuda_graph": True, "host": {"numa": numa, "cpu_count": os.cpu_count()}},
+        "data": "synthetic FashionMNIST-shape uint8 28x28 images + labels, random-init weights",
+        "impl": "ours-engine",
+        "config": _config(global_batch, B, world),
+        "arm": {"entry": "parallel.MLPTrainEngine.stage/step driven by hand (no trainer); device-timed loop rotates over "
+                         f"{rot} device-resident batches", "gradient_path": f"{args.algo}/{eng.ar_mode}", "cuda_graph": True,
+                "host": {"numa": numa, "cpu_count": os.cpu_count()}},
         "clocks": clk.summary(),
-        "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "ms_per_step": round(e2e_ms / K, 4),
-                "h2d_bytes_per_step": B * (784 + 8), "d2h_bytes_per_step": 4,
-                "api": "data.U8BatchLoader -> parallel.MLPTrainEngine.stage/step -> loss.copy_(pinned)"},
+        "repeats": R, "ms_per_step_min": round(ms_min / K, 4), "ms_per_step_max": round(ms_max / K, 4),
+        "e2e": {"value": round(global_batch * K / (e2e_ms / 1e3), 1), "unit": "samples/s", "ms_per_step": round(e2e_ms / K, 4),
+                "ms_per_step_min": round(e2e_min / K, 4), "ms_per_step_max": round(e2e_max / K, 4),
+                "h2d_bytes_per_step": loader.h2d_bytes_per_batch, "d2h_bytes_per_step": 4,
+                "window": "one loader epoch: joining the background shuffle of this epoch, per-step H2D, step, loss write-back",
+                "api": "data.U8BatchLoader -> parallel.MLPTrainEngine.stage/step -> loss ring in pinned host memory"},
         "gpu_launches": launches_per_step * K,
         "gpu_launches_per_step": launches_per_step,
         "tflops_fp32_equiv": round(flops / (ms / 1e3) / 1e12, 2),
@@ -266,20 +389,8 @@ def run_reference(args):
     steps_total = K + W
     # the reference hard-codes ~/data and a download; give it a HOME with synthetic idx files of the right shape
     home = os.path.join(ROOT, ".ref_home")                    # scratch inside the repo copy, ignored by git and gpurun
-    os.makedirs(home, exist_ok=True)
     os.environ["HOME"] = home
-    n_train = B * world * steps_total
-    marker = os.path.join(home, f"data_ready_{n_train}")
-    if rank == 0 and not os.path.exists(marker):
-        sys.path.insert(0, os.path.join(ROOT, "baseline"))
-        import make_idx
-        make_idx.write(os.path.join(home, "data"), n_train=n_train, n_test=max(256, world * 32))
-        open(marker, "w").close()
-    t_wait = time.time()
-    while not os.path.exists(marker):
-        time.sleep(0.2)
-        if time.time() - t_wait > 600:
-            raise SystemExit("timed out waiting for the synthetic dataset")
+    _write_dataset(home, n_train=B * world * steps_total, n_test=max(256, world * 32), rank=rank)
     sys.path.insert(0, os.path.join(ROOT, "baseline", "ray_standin"))
     sys.path.insert(0, ref_dir)
     for mod in [m for m in sys.modules if m.startswith("ray_torch_distributed_checkpoint_b200")]:
@@ -295,16 +406,20 @@ def run_reference(args):
     torch.cuda.synchronize(dev)
     rec = TIMING["records"]
     begins = [r for r in rec if r[0] == "step_begin"]
+    synced = [r for r in rec if r[0] == "step_begin_synced"]
     ends = [r for r in rec if r[0] == "step_end"]
     n = min(len(begins), len(ends))
     if n < W + K:
         K = max(1, n - W)
-    # kernel-side time of each timed step: begin event (recorded right before the step's launches, GPU idle
-    # while the reference's CPU loader ran) to end event (after optimizer.step())
-    dev_ms = sum(begins[i][2].elapsed_time(ends[i][2]) for i in range(W, W + K))
+    # kernel-side time of each timed step. `synced`: begin event recorded after a cross-rank barrier, i.e. once EVERY rank
+    # holds its batch, so a step's interval holds compute + NCCL only (at N >= 2 the plain begin event is recorded when
+    # THIS rank's CPU loader returns; the slowest peer's loader stall then shows up inside the NCCL all-reduce).
+    dev_ms_skew = sum(begins[i][2].elapsed_time(ends[i][2]) for i in range(W, W + K))
+    dev_ms = sum(synced[i][2].elapsed_time(ends[i][2]) for i in range(W, W + K)) if len(synced) >= W + K else dev_ms_skew
     # end to end: first timed batch handed to the loop -> last timed step finished, loader stalls included
     e2e_ms = begins[W][2].elapsed_time(ends[W + K - 1][2])
     dev_ms = _max_over_ranks(dev_ms, dev)
+    dev_ms_skew = _max_over_ranks(dev_ms_skew, dev)
     e2e_ms = _max_over_ranks(e2e_ms, dev)
     gb = B * world
     out = {
@@ -312,10 +427,12 @@ def run_reference(args):
         "warmup": W, "ms_per_step": round(dev_ms / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "fp32", "data": "synthetic FashionMNIST-shape idx files read by torchvision.datasets.FashionMNIST, random-init weights",
         "impl": "reference",
-        "config": {"model": MODEL, "global_batch": gb, "batch_per_gpu": B, "seq_len": None, "parallelism": f"dp{world}",
-                   "entry": "baseline/_ref/my_ray_module.py::train_fashion_mnist (unmodified) on a stock-torch stand-in for "
-                            "ray.train (torch DDP + NCCL + cuBLAS); value = sum of per-step device intervals (the "
-                            "reference's CPU DataLoader stalls excluded), e2e = loader included"},
+        "config": _config(gb, B, world),
+        "arm": {"entry": "baseline/_ref/my_ray_module.py::train_fashion_mnist (unmodified) on a stock-torch stand-in for "
+                         "ray.train (torch DDP + NCCL + cuBLAS); value = sum of per-step device intervals that start once every rank "
+                         "holds its batch (the reference's CPU DataLoader stalls excluded), e2e = loader included"},
+        "value_with_loader_skew": round(gb * K / (dev_ms_skew / 1e3), 1),
+        "ms_per_step_with_loader_skew": round(dev_ms_skew / K, 4),
         "clocks": clk.summary(),
         "e2e": {"value": round(gb * K / (e2e_ms / 1e3), 1), "unit": "samples/s", "ms_per_step": round(e2e_ms / K, 4),
                 "h2d_bytes_per_step": B * (784 * 4 + 8), "d2h_bytes_per_step": 0,
@@ -334,17 +451,22 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--impl", choices=["ours", "ours-engine", "reference"], default="ours")
+    ap.add_argument("--repeats", type=int, default=5, help="back-to-back K-step blocks timed (ours arms); the median block is reported")
     ap.add_argument("--batch-per-gpu", type=int, default=int(os.environ.get("RTDC_BENCH_BATCH", 18944)),
                     help="per-GPU batch; 18944 = 148 SMs x 128 rows, i.e. exactly two waves of 128x256 output tiles")
-    ap.add_argument("--rotate", type=int, default=4, help="distinct device-resident input batches for the device-timed loop")
-    ap.add_argument("--lookahead", type=int, default=3, help="H2D batches in flight ahead of the consumer (e2e loop)")
+    ap.add_argument("--val-size", type=int, default=10000, help="validation samples per epoch (ours arm)")
+    ap.add_argument("--rotate", type=int, default=4, help="distinct device-resident input batches for the device-timed loop (ours-engine)")
+    ap.add_argument("--lookahead", type=int, default=3, help="H2D batches in flight ahead of the consumer (ours-engine e2e loop)")
     ap.add_argument("--algo", default="auto", choices=["auto", "two_shot", "nvls"])
+    ap.add_argument("--ar-mode", default=None, choices=["fused", "merged", "bucketed"])
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.impl == "ours-engine":
+        run_ours_engine(args)
     else:
         run_ours(args)
 

@@ -3,10 +3,12 @@
 ``ray_torch_distributed_checkpoint_b200``.
 
 What differs from the reference on purpose (SURVEY.md §3.2 hot spots):
-* Linear+ReLU+Dropout chains, the loss and the optimizer run on the fused sm_100a kernels; the DDP
-  gradient all-reduce is the framework's NVLink kernel, overlapped with backward;
-* validation keeps its loss / correct-count accumulators on the device: one D2H per epoch instead of
-  two ``.item()`` syncs per batch (ref ``my_ray_module.py:168,170``);
+* on a GPU worker ``prepare_model`` recognises this network and backs it with the whole-step engine: the training
+  loop below — the reference's, line for line — replays ONE CUDA graph of the fused sm_100a kernels per step
+  (forward, loss, backward, NVLink gradient reduce-scatter + SGD + parameter multicast); ``prepare_data_loader`` keeps the
+  images as bytes in pinned memory and moves uint8 pixels and labels over PCIe;
+* validation keeps its loss / correct-count accumulators on the device (``nn.EvalAccumulator``): one D2H per epoch
+  instead of two ``.item()`` syncs per batch (ref ``my_ray_module.py:168,170``);
 * the checkpoint is snapshotted asynchronously (device copy -> pinned D2H on a side stream -> writer
   thread) and only rank 0 writes files; names, dict keys and the ``torch.save`` format are the reference's;
 * ``set_weights_from_checkpoint`` falls back to ``latest_model.pt`` when ``best_model.pt`` is absent in
@@ -26,7 +28,7 @@ from torch.utils.data import DataLoader
 import ray_torch_distributed_checkpoint_b200 as rtdc
 from ray_torch_distributed_checkpoint_b200 import ckpt, data, train
 from ray_torch_distributed_checkpoint_b200.models import NeuralNetwork
-from ray_torch_distributed_checkpoint_b200.nn import CrossEntropyLoss
+from ray_torch_distributed_checkpoint_b200.nn import CrossEntropyLoss, EvalAccumulator
 from ray_torch_distributed_checkpoint_b200.optim import SGD
 from ray_torch_distributed_checkpoint_b200.train import Checkpoint, CheckpointConfig, RunConfig, ScalingConfig
 from ray_torch_distributed_checkpoint_b200.train.torch import (TorchTrainer, get_device, prepare_data_loader,
@@ -126,7 +128,6 @@ def train_func_per_worker(config: Dict):
     if saved is not None and (resume is not None or exact_resume):
         optimizer.load_state_dict(saved["optimizer_state_dict"])
     checkpointer = ckpt.AsyncCheckpointer(device) if rank == 0 else None
-    on_gpu = device.type == "cuda"
 
     t0_full = time.time()
     for epoch in range(start_epoch, epochs):
@@ -142,21 +143,13 @@ def train_func_per_worker(config: Dict):
             optimizer.step()
 
         model.eval()
-        loss_sum = torch.zeros((), device=device)
-        correct = torch.zeros((), dtype=torch.int64, device=device)
-        num_total, num_batches = 0, 0
+        metrics = EvalAccumulator(model)                      # loss sum and correct count stay on the device
         with torch.no_grad():
             for X, y in val_loader:
                 pred = model(X)
-                if on_gpu:
-                    rtdc.ops.softmax_cross_entropy(pred, y, loss_sum_accum=loss_sum, correct_accum=correct)
-                else:
-                    loss_sum += torch.nn.functional.cross_entropy(pred, y)
-                    correct += (pred.argmax(1) == y).sum()
-                num_total += y.shape[0]
-                num_batches += 1
-        val_loss = float(loss_sum.item()) / max(1, num_batches)       # the epoch's only device->host sync
-        accuracy = int(correct.item()) / max(1, num_total)
+                loss = loss_fn(pred, y)
+                metrics.update(loss, pred, y)
+        val_loss, accuracy = metrics.compute()                # the epoch's only device->host sync
         val_losses.append(val_loss)
         val_acc.append(accuracy)
 

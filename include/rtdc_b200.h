@@ -163,6 +163,13 @@ int rtdc_u8_affine(const uint8_t* src, float* dst, size_t n, float scale, float 
  * tensor-bound kernel is paced down so that it does not fight that kernel for issue slots and L2 bandwidth. */
 int rtdc_u8_affine_paced(const uint8_t* src, float* dst, size_t n, float scale, float shift, int blocks, void* stream);
 
+/* ReLU(+inverted dropout) backward with padding in one pass: dz[r,c] = dy[r,c] * (y[r,c] > 0 ? scale : 0) for c < cols (y = the
+ * layer's output; y NULL copies dy), dz[r,c] = 0 for cols <= c < cols_out. Used for the last layer of a fused chain, whose
+ * gradient does not come out of a dgrad epilogue: cols_out rounds the row pitch up to what TMA needs (16 bytes).
+ * ref: autograd's threshold_backward + dropout backward behind my_ray_module.py:159 (K5/K6). */
+int rtdc_act_backward(const float* dy, int lddy, const float* y_or_null, int ldy, int rows, int cols, int cols_out, float scale,
+                      float* dz, int lddz, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Fused optimizer steps over a flat parameter arena (K7). hyper points to device memory so a
  * captured CUDA graph sees updated values.
@@ -175,6 +182,12 @@ int rtdc_sgd_step(float* p, const float* g, float* m, size_t n, const rtdc_sgd_h
  * one launch less per training step. hyper_dev->pad is the arrival counter: keep it 0 between calls. */
 int rtdc_sgd_step_advance(float* p, const float* g, float* m, size_t n, rtdc_sgd_hyper* hyper_dev, uint32_t* step_counter_or_null,
                           void* stream);
+/* Same again, and that last block also stores *loss_dev into loss_log_host[step_counter[0] % loss_log_slots] before it bumps the
+ * counter. loss_log_host is PINNED HOST memory (mapped into the device address space, e.g. cudaHostAlloc / a torch pinned
+ * tensor; loss_log_slots a power of two): every step's loss crosses PCIe by itself, so a host can follow the training loss
+ * without synchronising with the step stream or adding a copy to a captured graph. */
+int rtdc_sgd_step_advance_log(float* p, const float* g, float* m, size_t n, rtdc_sgd_hyper* hyper_dev, uint32_t* step_counter_or_null,
+                              const float* loss_dev_or_null, float* loss_log_host_or_null, uint32_t loss_log_slots, void* stream);
 /* Adam / AdamW (decoupled != 0): step counter lives in hyper_dev->step and is advanced by rtdc_adam_advance. */
 typedef struct rtdc_adam_hyper { float lr, beta1, beta2, eps, weight_decay, grad_scale; int decoupled; int step; } rtdc_adam_hyper;
 int rtdc_adam_step(float* p, const float* g, float* m, float* v, size_t n, const rtdc_adam_hyper* hyper_dev, void* stream);
@@ -192,7 +205,7 @@ int rtdc_counter_advance(uint32_t* counter_dev, rtdc_sgd_hyper* sgd_hyper_or_nul
  * (my_ray_module.py:135,244-250).
  */
 #define RTDC_SYMM_MAX_WORLD 8
-#define RTDC_SYMM_MAX_BLOCKS 64
+#define RTDC_SYMM_MAX_BLOCKS 160
 typedef struct rtdc_symm_info_t {
   int rank, world, device;
   size_t bytes;               /* usable bytes per rank */
@@ -220,6 +233,22 @@ int rtdc_symm_destroy(void* handle);
  * ref: the DDP gradient bucket all-reduce with its 1/world pre-scale (C3; my_ray_module.py:159). */
 int rtdc_symm_all_reduce(void* handle, size_t offset, size_t count, int dtype, float scale, int algo,
                          void* out_local, int max_blocks, void* stream);
+/* The distributed optimizer step as ONE kernel (replaces rtdc_symm_all_reduce + rtdc_sgd_step_advance): gradient, parameter
+ * and momentum arenas of `count` fp32 elements live at byte offsets g/p/m_offset of every rank's symmetric buffer. Rank r owns
+ * the r-th of `world` equal slices (in 16-byte vectors): it sums that slice of all ranks' gradients (algo 3: multimem.ld_reduce
+ * through the switch; algo 2: peer loads added in rank order), scales by 1/world, applies the SGD update of rtdc_sgd_hyper to
+ * its slice of parameters and momentum, and writes the new parameters into EVERY rank's parameter arena (multimem.st / peer
+ * stores). Per GPU that is count/world in and count/world out instead of an all-reduce's 2x, and 1/world of the optimizer
+ * math. Momentum is only maintained by the owner of a slice: rtdc_symm_gather_slices(m_offset, count) completes a rank's copy
+ * (checkpoints). Counter / first-step / loss-log handling as rtdc_sgd_step_advance_log. algo 0 = NVLS when bound and
+ * world > 2, else P2P. Every rank must call it in the same order as its other collectives on this handle.
+ * ref: DDP all-reduce (my_ray_module.py:159) + optimizer.step() (:160). */
+int rtdc_symm_sgd_step(void* handle, size_t g_offset, size_t p_offset, size_t m_offset, size_t count, int algo,
+                       rtdc_sgd_hyper* hyper_dev, uint32_t* step_counter_or_null, const float* loss_dev_or_null,
+                       float* loss_log_host_or_null, uint32_t loss_log_slots, int max_blocks, void* stream);
+/* Copy, for every other rank q, slice q of the `count`-element arena at `offset` from rank q's buffer into this rank's (no
+ * barrier, not a collective: the caller knows the owners are idle, see above). */
+int rtdc_symm_gather_slices(void* handle, size_t offset, size_t count, void* stream);
 /* Copy `bytes` at `offset` of rank `root`'s symmetric buffer into dst_local on every rank (C2/C4). */
 int rtdc_symm_broadcast(void* handle, size_t offset, size_t bytes, int root, void* dst_local, void* stream);
 /* Device-side barrier across ranks on the stream (C5). */

@@ -136,21 +136,52 @@ __device__ __forceinline__ void reduce_vec(const SymmView& sv, size_t byte_off, 
 }
 
 // ------------------------------------------------------------------ two-shot (in place)
+constexpr int AR_UNROLL = 4;   // 16-byte vectors per thread per trip (NVLS); the P2P kernels hold UNROLL x WORLD vectors in registers
+template <int WORLD> struct P2PUnroll { static constexpr int value = WORLD <= 4 ? 4 : 2; };
+
 template <typename T, int WORLD>
 __global__ void __launch_bounds__(AR_THREADS)
 two_shot_kernel(SymmView sv, size_t offset, size_t nvec_total, float scale) {
+  constexpr int U = P2PUnroll<WORLD>::value;
   const unsigned int e = epoch_begin(sv);
   group_barrier(sv, e + 1);  // every rank's contribution is in its buffer
   // slice owned by this rank, in 16-byte vectors
   const size_t per = (nvec_total + WORLD - 1) / WORLD;
   const size_t begin = min(nvec_total, per * sv.rank), end = min(nvec_total, begin + per);
-  for (size_t v = begin + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < end;
-       v += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const size_t off = offset + v * 16;
-    uint4 r;
-    reduce_vec<T, WORLD>(sv, off, scale, r);
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t v0 = begin + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < end; v0 += stride * U) {
+    uint4 raw[U][WORLD];
 #pragma unroll
-    for (int p = 0; p < WORLD; ++p) st_peer16(static_cast<char*>(sv.peers[(sv.rank + p) % WORLD]) + off, r);
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + u * stride;
+      if (v < end) {
+#pragma unroll
+        for (int p = 0; p < WORLD; ++p) raw[u][p] = ld_peer16(static_cast<const char*>(sv.peers[p]) + offset + v * 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + u * stride;
+      if (v >= end) continue;
+      constexpr int N = Pack<T>::N;
+      float acc[N];
+#pragma unroll
+      for (int i = 0; i < N; ++i) acc[i] = 0.f;
+#pragma unroll
+      for (int p = 0; p < WORLD; ++p) {  // fixed rank order
+        float f[N];
+        Pack<T>::load(&raw[u][p], f);
+#pragma unroll
+        for (int i = 0; i < N; ++i) acc[i] += f[i];
+      }
+#pragma unroll
+      for (int i = 0; i < N; ++i) acc[i] *= scale;
+      uint4 r;
+      Pack<T>::store(&r, acc);
+      const size_t off = offset + v * 16;
+#pragma unroll
+      for (int p = 0; p < WORLD; ++p) st_peer16(static_cast<char*>(sv.peers[(sv.rank + p) % WORLD]) + off, r);
+    }
   }
   group_barrier(sv, e + 2);  // all pushes into my buffer have landed
   epoch_end(sv, e, 2);
@@ -199,19 +230,131 @@ nvls_kernel(SymmView sv, size_t offset, size_t nvec_total, float scale) {
   const size_t per = (nvec_total + sv.world - 1) / sv.world;
   const size_t begin = min(nvec_total, per * sv.rank), end = min(nvec_total, begin + per);
   char* mc = static_cast<char*>(sv.mc) + offset;
-  for (size_t v = begin + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < end;
-       v += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    uint4 raw = multimem_ld_reduce<T>(mc + v * 16);
-    float f[N];
-    Pack<T>::load(&raw, f);
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t v0 = begin + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < end; v0 += stride * AR_UNROLL) {
+    uint4 raw[AR_UNROLL];
 #pragma unroll
-    for (int i = 0; i < N; ++i) f[i] *= scale;
-    Pack<T>::store(&raw, f);
-    multimem_st(mc + v * 16, raw);
+    for (int u = 0; u < AR_UNROLL; ++u)
+      if (v0 + u * stride < end) raw[u] = multimem_ld_reduce<T>(mc + (v0 + u * stride) * 16);
+#pragma unroll
+    for (int u = 0; u < AR_UNROLL; ++u) {
+      const size_t v = v0 + u * stride;
+      if (v >= end) continue;
+      float f[N];
+      Pack<T>::load(&raw[u], f);
+#pragma unroll
+      for (int i = 0; i < N; ++i) f[i] *= scale;
+      Pack<T>::store(&raw[u], f);
+      multimem_st(mc + v * 16, raw[u]);
+    }
   }
   __threadfence_system();
   group_barrier(sv, e + 2);
   epoch_end(sv, e, 2);
+}
+
+// ------------------------------------------------------------------ fused reduce-scatter + SGD + parameter multicast
+// One kernel per training step in place of {all-reduce, full-arena optimizer}: rank r owns vectors [r*per, (r+1)*per) of the
+// flat arenas. After the entry barrier (every rank's gradients are complete) it pulls the sum of its slice of the gradient
+// arena (NVLS: one multimem.ld_reduce per vector, the switch adds; P2P: one load per peer, added in rank order), applies
+// 1/world and the SGD/momentum update to its slice of the parameters (momentum exists only on the owner), and stores the new
+// parameters into EVERY replica's parameter arena (multimem.st, or one store per peer). The exit barrier makes all pushes
+// visible before any rank's next forward pass reads them. Replicas stay bit-identical because each element is computed once.
+// The last block to finish advances the step counter / first-step flag and logs the step's loss to pinned host memory.
+template <int WORLD, bool NVLS>
+__global__ void __launch_bounds__(AR_THREADS)
+sgd_fused_kernel(SymmView sv, size_t g_off, size_t p_off, size_t m_off, size_t nvec_total, float inv_world, rtdc_sgd_hyper* hp,
+                 uint32_t* step_counter, const float* loss, float* loss_log, uint32_t log_mask) {
+  constexpr int U = NVLS ? AR_UNROLL : P2PUnroll<WORLD>::value;
+  const unsigned int e = epoch_begin(sv);
+  const rtdc_sgd_hyper h = *hp;
+  group_barrier(sv, e + 1);
+  const int world = NVLS ? sv.world : WORLD;
+  const size_t per = (nvec_total + world - 1) / world;
+  const size_t begin = min(nvec_total, per * sv.rank), end = min(nvec_total, begin + per);
+  char* local = static_cast<char*>(sv.peers[sv.rank]);
+  char* mc = static_cast<char*>(sv.mc);
+  const bool use_m = h.momentum != 0.f;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t v0 = begin + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < end; v0 += stride * U) {
+    uint4 raw[U][WORLD];   // NVLS: one switch-reduced vector; P2P: one vector per peer, all in flight before the first add
+    float4 pv[U], mv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + u * stride;
+      if (v >= end) continue;
+      if (NVLS) {
+        raw[u][0] = multimem_ld_reduce<float>(mc + g_off + v * 16);
+      } else {
+#pragma unroll
+        for (int p = 0; p < WORLD; ++p) raw[u][p] = ld_peer16(static_cast<const char*>(sv.peers[p]) + g_off + v * 16);
+      }
+      pv[u] = *reinterpret_cast<const float4*>(local + p_off + v * 16);
+      mv[u] = use_m ? *reinterpret_cast<const float4*>(local + m_off + v * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + u * stride;
+      if (v >= end) continue;
+      float gg[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int p = 0; p < WORLD; ++p) {   // fixed rank order (one pass for NVLS)
+        float f[4];
+        Pack<float>::load(&raw[u][p], f);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) gg[j] += f[j];
+      }
+      float* pp = &pv[u].x;
+      float* mm = &mv[u].x;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float gr = gg[j] * inv_world * h.grad_scale + h.weight_decay * pp[j];
+        if (use_m) {
+          mm[j] = h.first_step ? gr : h.momentum * mm[j] + (1.f - h.dampening) * gr;
+          gr = h.nesterov ? gr + h.momentum * mm[j] : mm[j];
+        }
+        pp[j] -= h.lr * gr;
+      }
+      if (use_m) *reinterpret_cast<float4*>(local + m_off + v * 16) = mv[u];
+      const uint4 out = *reinterpret_cast<const uint4*>(&pv[u]);
+      if (NVLS) {
+        multimem_st(mc + p_off + v * 16, out);
+      } else {
+#pragma unroll
+        for (int p = 0; p < WORLD; ++p) st_peer16(static_cast<char*>(sv.peers[(sv.rank + p) % WORLD]) + p_off + v * 16, out);
+      }
+    }
+  }
+  if (NVLS) __threadfence_system();
+  group_barrier(sv, e + 2);
+  epoch_end(sv, e, 2);
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const int ticket = atomicAdd(&hp->pad, 1);
+    if (ticket == static_cast<int>(gridDim.x) - 1) {
+      hp->first_step = 0;
+      hp->pad = 0;
+      if (step_counter != nullptr) {
+        const uint32_t c = step_counter[0];
+        if (loss_log != nullptr && loss != nullptr) loss_log[c & log_mask] = *loss;
+        step_counter[0] = c + 1u;
+      }
+      __threadfence();
+    }
+  }
+}
+
+// Pull every other rank's slice of a sliced arena (the momentum of the fused step) into this rank's copy. No barrier: the
+// caller guarantees the owners are not writing (they cannot start the next step before this rank joins its entry barrier).
+__global__ void __launch_bounds__(AR_THREADS)
+gather_slices_kernel(SymmView sv, size_t offset, size_t nvec_total) {
+  const size_t per = (nvec_total + sv.world - 1) / sv.world;
+  char* local = static_cast<char*>(sv.peers[sv.rank]) + offset;
+  for (size_t v = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec_total; v += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int owner = static_cast<int>(v / per);
+    if (owner == sv.rank) continue;
+    reinterpret_cast<uint4*>(local)[v] = ld_peer16(static_cast<const char*>(sv.peers[owner]) + offset + v * 16);
+  }
 }
 
 // ------------------------------------------------------------------ broadcast / barrier
@@ -296,8 +439,10 @@ RTDC_API int rtdc_symm_all_reduce(void* handle, size_t offset, size_t count, int
   }
   // enough blocks to cover the owned slice, bounded by the signal-pad rows
   const size_t work = algo == 1 ? nvec : (nvec + info.world - 1) / info.world;
-  int blocks = static_cast<int>((work + AR_THREADS * 4 - 1) / (AR_THREADS * 4));
-  int cap = max_blocks > 0 ? max_blocks : 32;
+  int blocks = static_cast<int>((work + AR_THREADS * AR_UNROLL - 1) / (AR_THREADS * AR_UNROLL));
+  // latency-bound sizes (the MLP's buckets) want few blocks (fewer barrier participants); bandwidth-bound ones want the links
+  // saturated: ~1 block per SM
+  int cap = max_blocks > 0 ? max_blocks : (count * esize >= (8u << 20) ? RTDC_SYMM_MAX_BLOCKS : 32);
   if (cap > RTDC_SYMM_MAX_BLOCKS) cap = RTDC_SYMM_MAX_BLOCKS;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
@@ -329,6 +474,70 @@ RTDC_API int rtdc_symm_barrier(void* handle, void* stream) {
   int rc = view_of(handle, &sv, &info);
   if (rc != RTDC_OK) return rc;
   barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(sv);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
+RTDC_API int rtdc_symm_sgd_step(void* handle, size_t g_offset, size_t p_offset, size_t m_offset, size_t count, int algo,
+                                rtdc_sgd_hyper* hyper_dev, uint32_t* step_counter_or_null, const float* loss_dev_or_null,
+                                float* loss_log_host_or_null, uint32_t loss_log_slots, int max_blocks, void* stream) {
+  SymmView sv;
+  rtdc_symm_info_t info;
+  int rc = view_of(handle, &sv, &info);
+  if (rc != RTDC_OK) return rc;
+  if (!hyper_dev) return fail(RTDC_ERR_ARG, "symm_sgd_step: null hyper-parameter pointer");
+  if ((g_offset | p_offset | m_offset) % 16 != 0 || count % 4 != 0)
+    return fail(RTDC_ERR_ARG, "symm_sgd_step: offsets must be multiples of 16 bytes and count a multiple of 4 elements");
+  const size_t bytes = count * 4;
+  if (g_offset + bytes > info.bytes || p_offset + bytes > info.bytes || m_offset + bytes > info.bytes)
+    return fail(RTDC_ERR_LIMIT, "symm_sgd_step: an arena exceeds the symmetric buffer (%zu bytes)", info.bytes);
+  if (loss_log_slots & (loss_log_slots - 1)) return fail(RTDC_ERR_ARG, "symm_sgd_step: loss_log_slots must be a power of two");
+  if (count == 0) return RTDC_OK;
+  if (algo == 0) algo = (info.multicast_ptr && info.world > 2) ? 3 : 2;
+  if (algo == 3 && !info.multicast_ptr) return fail(RTDC_ERR_ARG, "symm_sgd_step: NVLS requested but multicast is not available");
+  if (algo != 2 && algo != 3) return fail(RTDC_ERR_ARG, "symm_sgd_step: algo must be 0 (auto), 2 (P2P) or 3 (NVLS)");
+  const size_t nvec = count / 4;
+  const size_t work = (nvec + info.world - 1) / info.world;
+  int blocks = static_cast<int>((work + AR_THREADS - 1) / AR_THREADS);   // one vector per thread when the pad rows allow it
+  int cap = max_blocks > 0 ? max_blocks : RTDC_SYMM_MAX_BLOCKS;
+  if (cap > RTDC_SYMM_MAX_BLOCKS) cap = RTDC_SYMM_MAX_BLOCKS;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const float inv_world = 1.0f / static_cast<float>(info.world);
+  const uint32_t mask = loss_log_slots ? loss_log_slots - 1 : 0;
+  float* log = loss_log_slots ? loss_log_host_or_null : nullptr;
+#define RTDC_SGD_CASE(W)                                                                                                  \
+  case W:                                                                                                                 \
+    sgd_fused_kernel<W, false><<<blocks, AR_THREADS, 0, st>>>(sv, g_offset, p_offset, m_offset, nvec, inv_world, hyper_dev, \
+                                                              step_counter_or_null, loss_dev_or_null, log, mask);         \
+    break;
+  if (algo == 3) {
+    sgd_fused_kernel<1, true><<<blocks, AR_THREADS, 0, st>>>(sv, g_offset, p_offset, m_offset, nvec, inv_world, hyper_dev,
+                                                             step_counter_or_null, loss_dev_or_null, log, mask);
+  } else {
+    switch (info.world) {
+      RTDC_SGD_CASE(1) RTDC_SGD_CASE(2) RTDC_SGD_CASE(3) RTDC_SGD_CASE(4) RTDC_SGD_CASE(5) RTDC_SGD_CASE(6) RTDC_SGD_CASE(7) RTDC_SGD_CASE(8)
+      default: return fail(RTDC_ERR_LIMIT, "symm_sgd_step supports world sizes 1..8 (got %d)", info.world);
+    }
+  }
+#undef RTDC_SGD_CASE
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
+RTDC_API int rtdc_symm_gather_slices(void* handle, size_t offset, size_t count, void* stream) {
+  SymmView sv;
+  rtdc_symm_info_t info;
+  int rc = view_of(handle, &sv, &info);
+  if (rc != RTDC_OK) return rc;
+  if (offset % 16 != 0 || count % 4 != 0) return fail(RTDC_ERR_ARG, "gather_slices: offset must be a multiple of 16 bytes and count of 4 elements");
+  if (offset + count * 4 > info.bytes) return fail(RTDC_ERR_LIMIT, "gather_slices: range exceeds the symmetric buffer");
+  if (count == 0 || info.world == 1) return RTDC_OK;
+  const size_t nvec = count / 4;
+  int blocks = static_cast<int>((nvec + AR_THREADS * 4 - 1) / (AR_THREADS * 4));
+  if (blocks > 148) blocks = 148;
+  gather_slices_kernel<<<blocks, AR_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(sv, offset, nvec);
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;
 }

@@ -309,7 +309,7 @@ u8_normalize_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst, si
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, size_t n,
-           rtdc_sgd_hyper* hp, uint32_t* step_counter, int advance) {
+           rtdc_sgd_hyper* hp, uint32_t* step_counter, int advance, const float* loss, float* loss_log, uint32_t log_mask) {
   const rtdc_sgd_hyper h = *hp;
   const size_t nvec = n / 4;
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
@@ -352,7 +352,11 @@ sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict
       if (ticket == static_cast<int>(gridDim.x) - 1) {
         hp->first_step = 0;
         hp->pad = 0;
-        if (step_counter != nullptr) step_counter[0] += 1u;
+        if (step_counter != nullptr) {
+          const uint32_t c = step_counter[0];
+          if (loss_log != nullptr && loss != nullptr) loss_log[c & log_mask] = *loss;   // pinned host ring: this step's loss
+          step_counter[0] = c + 1u;
+        }
         __threadfence();
       }
     }
@@ -394,6 +398,24 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   }
   if (blockIdx.x == 0) {
     for (size_t i = nvec * 4 + threadIdx.x; i < n; i += blockDim.x) adam_update(p[i], g[i], m[i], v[i], h, bc1, bc2_sqrt);
+  }
+}
+
+// dz[r, c] = dy[r, c] * (y[r, c] > 0 ? scale : 0) for c < cols, 0 for cols <= c < cols_out: the ReLU(+dropout) backward of a
+// layer whose gradient does not come out of a fused dgrad epilogue (the last layer of a chain), written with the padded row
+// pitch the TMA-fed wgrad/dgrad GEMMs need.
+__global__ void __launch_bounds__(256)
+act_backward_kernel(const float* __restrict__ dy, int lddy, const float* __restrict__ y, int ldy, int rows, int cols, int cols_out,
+                    float scale, float* __restrict__ dz, int lddz) {
+  const size_t total = static_cast<size_t>(rows) * cols_out;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / cols_out), c = static_cast<int>(i % cols_out);
+    float v = 0.f;
+    if (c < cols) {
+      v = dy[static_cast<size_t>(r) * lddy + c];
+      if (y != nullptr) v = y[static_cast<size_t>(r) * ldy + c] > 0.f ? v * scale : 0.f;
+    }
+    dz[static_cast<size_t>(r) * lddz + c] = v;
   }
 }
 
@@ -551,6 +573,17 @@ RTDC_API int rtdc_u8_affine(const uint8_t* src, float* dst, size_t n, float scal
   return RTDC_OK;
 }
 
+RTDC_API int rtdc_act_backward(const float* dy, int lddy, const float* y_or_null, int ldy, int rows, int cols, int cols_out, float scale,
+                               float* dz, int lddz, void* stream) {
+  if (!dy || !dz) return fail(RTDC_ERR_ARG, "act_backward: null pointer");
+  if (rows <= 0 || cols <= 0 || cols_out < cols || lddz < cols_out || lddy < cols || (y_or_null && ldy < cols))
+    return fail(RTDC_ERR_ARG, "act_backward: bad shape (rows %d cols %d cols_out %d)", rows, cols, cols_out);
+  act_backward_kernel<<<grid_for(static_cast<size_t>(rows) * cols_out, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      dy, lddy, y_or_null, ldy, rows, cols, cols_out, scale, dz, lddz);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
 RTDC_API int rtdc_u8_affine_paced(const uint8_t* src, float* dst, size_t n, float scale, float shift, int blocks, void* stream) {
   if (!src || !dst) return fail(RTDC_ERR_ARG, "u8_affine: null pointer");
   if (n == 0) return RTDC_OK;
@@ -602,12 +635,15 @@ RTDC_API int rtdc_fold_input_bias(const float* w, int ldw, int rows, int cols, c
   return RTDC_OK;
 }
 
-static int sgd_launch(float* p, const float* g, float* m, size_t n, rtdc_sgd_hyper* hyper_dev, uint32_t* counter, int advance, void* stream) {
+static int sgd_launch(float* p, const float* g, float* m, size_t n, rtdc_sgd_hyper* hyper_dev, uint32_t* counter, int advance, void* stream,
+                      const float* loss = nullptr, float* loss_log = nullptr, uint32_t log_slots = 0) {
+  if (log_slots & (log_slots - 1)) return fail(RTDC_ERR_ARG, "sgd_step: loss_log_slots must be a power of two");
   if (!p || !g || !hyper_dev) return fail(RTDC_ERR_ARG, "sgd_step: null pointer");
   if (n == 0) return RTDC_OK;
   if ((reinterpret_cast<uintptr_t>(p) & 15u) || (reinterpret_cast<uintptr_t>(g) & 15u) || (reinterpret_cast<uintptr_t>(m) & 15u))
     return fail(RTDC_ERR_ARG, "sgd_step: arenas must be 16-byte aligned");
-  sgd_kernel<<<grid_for(n / 4 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, n, hyper_dev, counter, advance);
+  sgd_kernel<<<grid_for(n / 4 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, n, hyper_dev, counter, advance, loss,
+                                                                                        log_slots ? loss_log : nullptr, log_slots ? log_slots - 1 : 0);
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;
 }
@@ -619,6 +655,11 @@ RTDC_API int rtdc_sgd_step(float* p, const float* g, float* m, size_t n, const r
 RTDC_API int rtdc_sgd_step_advance(float* p, const float* g, float* m, size_t n, rtdc_sgd_hyper* hyper_dev, uint32_t* step_counter_or_null,
                                    void* stream) {
   return sgd_launch(p, g, m, n, hyper_dev, step_counter_or_null, 1, stream);
+}
+
+RTDC_API int rtdc_sgd_step_advance_log(float* p, const float* g, float* m, size_t n, rtdc_sgd_hyper* hyper_dev, uint32_t* step_counter_or_null,
+                                       const float* loss_dev_or_null, float* loss_log_host_or_null, uint32_t loss_log_slots, void* stream) {
+  return sgd_launch(p, g, m, n, hyper_dev, step_counter_or_null, 1, stream, loss_dev_or_null, loss_log_host_or_null, loss_log_slots);
 }
 
 RTDC_API int rtdc_adam_step(float* p, const float* g, float* m, float* v, size_t n, const rtdc_adam_hyper* hyper_dev, void* stream) {

@@ -50,6 +50,8 @@ def main(payload_path: str) -> int:
         session.drain()
         if use_gpu:
             torch.cuda.synchronize()
+        from ..data.loader import dump_timing
+        dump_timing(rank)
         from ..ckpt import async_writer
         async_writer.wait_all()
         if world > 1:

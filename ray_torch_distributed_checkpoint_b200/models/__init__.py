@@ -2,9 +2,9 @@
 (ResNet-50, GPT-2 small). ``fused`` holds the modules that route Linear(+ReLU+Dropout) chains
 through the tcgen05 kernels."""
 from .mlp import NeuralNetwork, mlp_flops_per_sample
-from .fused import FusedLinearAct, fuse_linear_chains
+from .fused import fuse_linear_chains
 
-__all__ = ["NeuralNetwork", "mlp_flops_per_sample", "FusedLinearAct", "fuse_linear_chains", "resnet50", "GPT2", "GPT2Config"]
+__all__ = ["NeuralNetwork", "mlp_flops_per_sample", "fuse_linear_chains", "resnet50", "GPT2", "GPT2Config"]
 
 
 def __getattr__(name):

@@ -33,6 +33,13 @@ class _FusedCE(torch.autograd.Function):
         return dz * grad_out, None
 
 
+def __getattr__(name):
+    if name == "EvalAccumulator":
+        from .parallel.engine_api import EvalAccumulator
+        return EvalAccumulator
+    raise AttributeError(name)
+
+
 class CrossEntropyLoss(nn.Module):
     def __init__(self, reduction: str = "mean"):
         super().__init__()
@@ -41,6 +48,10 @@ class CrossEntropyLoss(nn.Module):
         self.reduction = reduction
 
     def forward(self, logits: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        from .parallel.engine_api import LazyLogits
+        if isinstance(logits, LazyLogits):
+            # engine-backed model: hand the batch to the fused step (training) or run the fused eval graph (eval mode)
+            return logits.owner._loss(logits, target)
         if (logits.is_cuda and logits.dtype == torch.float32 and logits.dim() == 2 and logits.shape[1] <= 32
                 and target.dtype == torch.int64 and target.dim() == 1):
             return _FusedCE.apply(logits, target.contiguous())

@@ -83,9 +83,13 @@ def _declare(lib):
     lib.rtdc_u8_affine_paced.argtypes = [vp, vp, sz, f, f, i, vp]
     lib.rtdc_u8_affine_paced.restype = i
     lib.rtdc_fold_input_bias.argtypes = [vp, i, i, i, vp, f, vp, vp]
+    lib.rtdc_act_backward.argtypes = [vp, i, vp, i, i, i, i, f, vp, i, vp]
+    lib.rtdc_act_backward.restype = i
     lib.rtdc_sgd_step.argtypes = [vp, vp, vp, sz, vp, vp]
     lib.rtdc_sgd_step_advance.argtypes = [vp, vp, vp, sz, vp, vp, vp]
     lib.rtdc_sgd_step_advance.restype = i
+    lib.rtdc_sgd_step_advance_log.argtypes = [vp, vp, vp, sz, vp, vp, vp, vp, C.c_uint32, vp]
+    lib.rtdc_sgd_step_advance_log.restype = i
     lib.rtdc_adam_step.argtypes = [vp, vp, vp, vp, sz, vp, vp]
     lib.rtdc_adam_advance.argtypes = [vp, vp]
     lib.rtdc_counter_advance.argtypes = [vp, vp, vp]

@@ -91,6 +91,24 @@ def colsum(x: torch.Tensor, *, cols: Optional[int] = None, out: Optional[torch.T
     return out
 
 
+def act_backward(dy: torch.Tensor, y: Optional[torch.Tensor], *, scale: float = 1.0, cols_out: Optional[int] = None,
+                 out: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
+    """``dz = dy * (y > 0) * scale`` (ReLU / inverted-dropout backward; ``y`` None: plain copy), written ``cols_out`` wide with
+    zero padding so the row pitch suits the TMA-fed GEMMs that consume it."""
+    if dy.dtype != torch.float32 or not dy.is_cuda or dy.dim() != 2 or dy.stride(1) != 1:
+        raise ValueError("dy must be a 2-D float32 CUDA tensor with unit inner stride")
+    if y is not None and (y.dtype != torch.float32 or y.shape != dy.shape or y.stride(1) != 1):
+        raise ValueError("y must match dy")
+    rows, cols = dy.shape
+    cols_out = cols if cols_out is None else cols_out
+    if out is None:
+        out = torch.empty(rows, cols_out, dtype=torch.float32, device=dy.device)
+    _lib.check(_lib.load().rtdc_act_backward(dy.data_ptr(), dy.stride(0), y.data_ptr() if y is not None else None,
+                                             y.stride(0) if y is not None else 0, rows, cols, cols_out, float(scale),
+                                             out.data_ptr(), out.stride(0), _lib.stream_ptr(stream)))
+    return out
+
+
 def u8_normalize(src: torch.Tensor, *, mean: float = 0.5, std: float = 0.5, out: Optional[torch.Tensor] = None,
                  stream=None) -> torch.Tensor:
     """uint8 pixels -> float32 ``(x/255 - mean)/std``, any shape (contiguous)."""
@@ -150,17 +168,25 @@ class SgdState:
 
 
 def sgd_step(p: torch.Tensor, g: torch.Tensor, m: Optional[torch.Tensor], state: SgdState, stream=None, *,
-             advance: bool = False, counter: Optional[torch.Tensor] = None):
+             advance: bool = False, counter: Optional[torch.Tensor] = None, loss: Optional[torch.Tensor] = None,
+             loss_log: Optional[torch.Tensor] = None):
     """One fused SGD(+momentum) step over flat fp32 arenas (in place on ``p`` and ``m``). ``advance``: the kernel also
-    clears ``first_step`` and adds 1 to ``counter`` (what :func:`counter_advance` does in its own launch)."""
+    clears ``first_step`` and adds 1 to ``counter`` (what :func:`counter_advance` does in its own launch); with ``loss``
+    (device scalar) and ``loss_log`` (pinned host ring, power-of-two length) it also stores the step's loss into
+    ``loss_log[counter % len]`` straight over PCIe."""
     n = p.numel()
     if g.numel() != n or (m is not None and m.numel() != n):
         raise ValueError("arena sizes differ")
     lib = _lib.load()
     mp = m.data_ptr() if m is not None else p.data_ptr()
     if advance:
-        _lib.check(lib.rtdc_sgd_step_advance(p.data_ptr(), g.data_ptr(), mp, n, state.dev.data_ptr(),
-                                             counter.data_ptr() if counter is not None else None, _lib.stream_ptr(stream)))
+        if loss_log is not None and not loss_log.is_pinned():
+            raise ValueError("loss_log must be pinned host memory")
+        _lib.check(lib.rtdc_sgd_step_advance_log(p.data_ptr(), g.data_ptr(), mp, n, state.dev.data_ptr(),
+                                                 counter.data_ptr() if counter is not None else None,
+                                                 loss.data_ptr() if loss is not None else None,
+                                                 loss_log.data_ptr() if loss_log is not None else None,
+                                                 loss_log.numel() if loss_log is not None else 0, _lib.stream_ptr(stream)))
         state.host.first_step = 0
     else:
         _lib.check(lib.rtdc_sgd_step(p.data_ptr(), g.data_ptr(), mp, n, state.dev.data_ptr(), _lib.stream_ptr(stream)))

@@ -95,10 +95,23 @@ class _FlatOptimizer:
 
 
 class SGD(_FlatOptimizer):
+    def __new__(cls, model_or_params, *args, **kwargs):
+        # an engine-backed model (train.torch.prepare_model on the reference network) steps through the fused engine
+        from .parallel.engine_api import EngineModel, EngineSGD, owner_of
+        owner = model_or_params if isinstance(model_or_params, EngineModel) else None
+        if owner is None and not isinstance(model_or_params, nn.Module):
+            model_or_params = list(model_or_params)
+            owner = owner_of(model_or_params)
+        if owner is not None:
+            return EngineSGD(owner, *args, **kwargs)
+        self = super().__new__(cls)
+        self._params_arg = model_or_params
+        return self
+
     def __init__(self, model_or_params, lr: float = 1e-3, momentum: float = 0.0, dampening: float = 0.0,
                  weight_decay: float = 0.0, nesterov: bool = False):
-        super().__init__(model_or_params, dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay,
-                                               nesterov=nesterov))
+        super().__init__(self._params_arg, dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay,
+                                                nesterov=nesterov))
         self.m_arena = torch.zeros_like(self.p_arena) if momentum != 0 else None
         self._steps = 0
         self.state_dev = ops.SgdState(self.device, lr, momentum, dampening, weight_decay, nesterov) if self.use_kernels else None

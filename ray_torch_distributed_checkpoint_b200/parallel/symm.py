@@ -40,8 +40,10 @@ def _declare(lib):
     lib.rtdc_symm_all_reduce.argtypes = [vp, sz, sz, i, f, i, vp, i, vp]
     lib.rtdc_symm_broadcast.argtypes = [vp, sz, sz, i, vp, vp]
     lib.rtdc_symm_barrier.argtypes = [vp, vp]
+    lib.rtdc_symm_sgd_step.argtypes = [vp, sz, sz, sz, sz, i, vp, vp, vp, vp, C.c_uint32, i, vp]
+    lib.rtdc_symm_gather_slices.argtypes = [vp, sz, sz, vp]
     for n in ("rtdc_symm_create", "rtdc_symm_bind_multicast", "rtdc_symm_info", "rtdc_symm_destroy",
-              "rtdc_symm_all_reduce", "rtdc_symm_broadcast", "rtdc_symm_barrier"):
+              "rtdc_symm_all_reduce", "rtdc_symm_broadcast", "rtdc_symm_barrier", "rtdc_symm_sgd_step", "rtdc_symm_gather_slices"):
         getattr(lib, n).restype = i
     lib._symm_declared = True
     return lib
@@ -127,6 +129,33 @@ class SymmetricArena:
         _lib.check(self.lib.rtdc_symm_all_reduce(self.handle, offset, numel, dt, scale, a,
                                                  out.data_ptr() if out is not None else None, max_blocks,
                                                  _lib.stream_ptr(stream)))
+
+    def sgd_step(self, g_offset: int, p_offset: int, m_offset: int, numel: int, state, *, counter: Optional[torch.Tensor] = None,
+                 loss: Optional[torch.Tensor] = None, loss_log: Optional[torch.Tensor] = None, algo="auto", max_blocks: int = 0,
+                 stream=None):
+        """The distributed optimizer step in one kernel: reduce-scatter of the gradient arena (through the switch with
+        NVLS, else peer loads), SGD/momentum on this rank's 1/world slice, updated parameters stored into every replica
+        (``rtdc_symm_sgd_step``). ``state`` is an ``ops.SgdState``; offsets are byte offsets of fp32 arenas of ``numel``
+        elements inside this arena."""
+        a = _ALGO_NAMES[algo] if isinstance(algo, str) else int(algo)
+        if a == ALGO_NVLS and not self.has_multicast:
+            raise RuntimeError("NVLS requested but multicast is unavailable on this system")
+        if a == ALGO_AUTO:
+            a = ALGO_NVLS if (self.has_multicast and self.world > 2) else ALGO_TWO_SHOT
+        if loss_log is not None and not loss_log.is_pinned():
+            raise ValueError("loss_log must be pinned host memory")
+        _lib.check(self.lib.rtdc_symm_sgd_step(self.handle, g_offset, p_offset, m_offset, numel, a, state.dev.data_ptr(),
+                                               counter.data_ptr() if counter is not None else None,
+                                               loss.data_ptr() if loss is not None else None,
+                                               loss_log.data_ptr() if loss_log is not None else None,
+                                               loss_log.numel() if loss_log is not None else 0, max_blocks,
+                                               _lib.stream_ptr(stream)))
+        state.host.first_step = 0
+
+    def gather_slices(self, offset: int, numel: int, stream=None):
+        """Complete this rank's copy of a rank-sliced fp32 arena (e.g. the momentum of :meth:`sgd_step`) by pulling the other
+        ranks' slices over NVLink. Not a collective."""
+        _lib.check(self.lib.rtdc_symm_gather_slices(self.handle, offset, numel, _lib.stream_ptr(stream)))
 
     def broadcast(self, offset: int, nbytes: int, root: int, dst: torch.Tensor, stream=None):
         _lib.check(self.lib.rtdc_symm_broadcast(self.handle, offset, nbytes, root, dst.data_ptr(), _lib.stream_ptr(stream)))

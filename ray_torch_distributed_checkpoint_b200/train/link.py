@@ -126,20 +126,28 @@ class SpmdLink:
         self.rank, self.world_size = rank, world_size
         self.on_complete = on_complete       # rank 0 only: (index, per-rank reports) -> has_checkpoint
         self._ckpt_flags: Dict[int, bool] = {}
+        # Reports may run on a background thread (checkpoint_upload_mode="async") while the main thread issues gradient
+        # collectives on the default group: collectives from two threads on ONE group can be ordered differently on
+        # different ranks. The report traffic therefore gets a gloo group of its own (collective call: every rank
+        # constructs the link at the same point of fit()).
+        self.group = None
+        if world_size > 1:
+            import torch.distributed as dist
+            self.group = dist.new_group(backend="gloo")
 
     def report(self, rank: int, index: int, metrics: Dict[str, Any], checkpoint_path: Optional[str]):
         import torch.distributed as dist
         entry = {"rank": rank, "index": index, "metrics": metrics, "checkpoint_path": checkpoint_path}
         if self.world_size > 1:
             gathered: List[Optional[dict]] = [None] * self.world_size if rank == 0 else None
-            dist.gather_object(entry, gathered, dst=0)
+            dist.gather_object(entry, gathered, dst=0, group=self.group)
         else:
             gathered = [entry]
         flag = [False]
         if rank == 0:
             flag[0] = bool(self.on_complete(index, gathered))
         if self.world_size > 1:
-            dist.broadcast_object_list(flag, src=0)     # doubles as the release barrier
+            dist.broadcast_object_list(flag, src=0, group=self.group)     # doubles as the release barrier
         self._ckpt_flags[index] = flag[0]
 
     def any_checkpoint(self, index: int) -> bool:
@@ -147,4 +155,12 @@ class SpmdLink:
 
     def done(self): pass
     def error(self, tb: str): pass
-    def close(self): pass
+
+    def close(self):
+        if self.group is not None:
+            import torch.distributed as dist
+            try:
+                dist.destroy_process_group(self.group)
+            except Exception:
+                pass
+            self.group = None

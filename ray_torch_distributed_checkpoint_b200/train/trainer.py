@@ -281,15 +281,19 @@ class TorchTrainer:
         try:
             _call_train_fn(self.train_loop_per_worker, self.train_loop_config)
             session.drain()
+            from ..data.loader import dump_timing
+            dump_timing(rank)
         except Exception as e:     # surface through Result like the driver mode does
             error = e
             raise
         finally:
             _set_session(None)
+            if error is None:
+                link.close()
+            payload = [book.result() if book else None]
+            if error is None and world > 1 and dist.is_initialized():
+                dist.broadcast_object_list(payload, src=0)      # every rank returns the Result, before the group goes away
             if created_pg and error is None:
                 dist.barrier()
                 dist.destroy_process_group()
-        payload = [book.result() if book else None]
-        if world > 1 and dist.is_initialized():
-            dist.broadcast_object_list(payload, src=0)
         return payload[0] if payload[0] is not None else Result(metrics=None, checkpoint=None, path=storage.trial_path)

@@ -125,28 +125,79 @@ def check_engine(rank, world, dev):
     from ray_torch_distributed_checkpoint_b200.models import NeuralNetwork
     from ray_torch_distributed_checkpoint_b200.parallel.engine import MLPTrainEngine
     B = 512
-    finals = {}
-    for mode in ("merged", "bucketed"):
+    finals, moms = {}, {}
+    modes = [("fused", "auto"), ("fused", "two_shot"), ("merged", "auto"), ("bucketed", "auto")]
+    for mode, algo in modes:
         torch.manual_seed(3 + rank)
-        eng = MLPTrainEngine(NeuralNetwork(), batch_size=B, lr=0.05, device=dev, seed=11, ar_mode=mode)
+        eng = MLPTrainEngine(NeuralNetwork(), batch_size=B, lr=0.05, device=dev, seed=11, ar_mode=mode, algo=algo)
         losses = []
         for step in range(6):
             g = torch.Generator(device=dev).manual_seed(50 * step + rank)
             x = torch.randint(0, 256, (B, 784), dtype=torch.uint8, device=dev, generator=g)
             y = torch.randint(0, 10, (B,), device=dev, generator=g)
             losses.append(eng.step(x, y).item())
+            if mode == "fused" and step == 3 and rank == 0:
+                # one rank alone (a checkpoint on rank 0) completes its momentum out of the owners' slices; no collective
+                m3 = [v["momentum_buffer"].clone() for v in eng.optimizer_state_dict()["state"].values()]
+                assert all(float(t.abs().sum()) > 0 for t in m3)
         ws = [torch.empty_like(eng.p_arena) for _ in range(world)]
         dist.all_gather(ws, eng.p_arena)
-        assert all(torch.equal(ws[0], w) for w in ws), f"engine replicas diverged ({mode})"
+        assert all(torch.equal(ws[0], w) for w in ws), f"engine replicas diverged ({mode}/{algo})"
         assert list(eng.model_state_dict())[0].startswith("module.")
         assert losses[-1] == losses[-1]
-        finals[mode] = eng.p_arena.clone()
+        assert eng.core.recent_losses(6) == losses                # every step's loss reached the pinned host ring
+        finals[(mode, algo)] = eng.p_arena.clone()
+        torch.cuda.synchronize()
+        dist.barrier()
+        moms[(mode, algo)] = torch.cat([v["momentum_buffer"].reshape(-1) for v in eng.optimizer_state_dict()["state"].values()]).clone()
+        torch.cuda.synchronize()
+        dist.barrier()
         eng.close()
-    # one all-reduce of the whole arena or one per bucket: the same sums (the in-switch NVLS reduction need not add in
-    # the same order for both, so compare to rounding rather than bit for bit)
-    assert torch.allclose(finals["merged"], finals["bucketed"], rtol=1e-5, atol=1e-7), "merged and bucketed reductions disagree"
+    # reduce-scatter + sharded SGD + parameter multicast, one all-reduce of the whole arena, one all-reduce per bucket: the
+    # same update (the in-switch NVLS reduction need not add in the same order as the P2P kernels, so compare to rounding)
+    ref = finals[("merged", "auto")]
+    for k, v in finals.items():
+        assert torch.allclose(v, ref, rtol=1e-5, atol=1e-7), f"{k} disagrees with the merged all-reduce"
+        assert torch.allclose(moms[k], moms[("merged", "auto")], rtol=1e-4, atol=1e-7), f"{k}: gathered momentum disagrees"
     if rank == 0:
-        print(f"[mgpu] engine ok (losses {losses[0]:.4f} -> {losses[-1]:.4f})", flush=True)
+        print(f"[mgpu] engine ok (losses {losses[0]:.4f} -> {losses[-1]:.4f}; modes {[m + '/' + a for m, a in modes]})", flush=True)
+
+
+def check_trainer(rank, world, dev):
+    """The reference-shaped program under this launch (SPMD mode of TorchTrainer.fit): engine-backed model, sharded uint8
+    loader, per-epoch checkpoint from rank 0, retention, warm start."""
+    import importlib
+    import tempfile
+    os.environ.update(RTDC_TRAIN_SIZE="16384", RTDC_TEST_SIZE="4096", RTDC_SYNTHETIC_DATA="1")
+    sys.path.insert(0, os.path.join(ROOT, "examples"))
+    import my_module
+    importlib.reload(my_module)
+    box = [tempfile.mkdtemp(prefix="rtdc_mgpu_trainer_") if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    result = my_module.train_fashion_mnist(num_workers=world, use_gpu=True, global_batch_size=256 * world, learning_rate=0.05,
+                                           epochs=3, checkpoint_storage_path=box[0])
+    assert result.error is None and result.metrics["training_iteration"] == 3
+    hist = result.metrics_dataframe
+    assert hist["val_loss"].iloc[-1] < hist["val_loss"].iloc[0]
+    if rank == 0:
+        kept = sorted(d for d in os.listdir(result.path) if d.startswith("checkpoint_"))
+        assert kept == ["checkpoint_000001", "checkpoint_000002"], kept
+        with result.checkpoint.as_directory() as d:
+            sd = torch.load(os.path.join(d, "latest_model.pt"), weights_only=True)
+        assert list(sd["model_state_dict"])[0] == "module.linear_relu_stack.0.weight"
+        assert all(float(v["momentum_buffer"].abs().sum()) > 0 for v in sd["optimizer_state_dict"]["state"].values())
+    dist.barrier()
+    again = my_module.train_fashion_mnist(num_workers=world, use_gpu=True, global_batch_size=256 * world, learning_rate=0.05,
+                                          epochs=1, checkpoint_storage_path=box[0], checkpoint=result.checkpoint)
+    assert again.metrics["val_loss"] < hist["val_loss"].iloc[0]
+    if rank == 0:
+        pred = my_module.TorchPredictor(result.checkpoint)
+        ds = my_module.get_dataloaders(512, val_only=True, as_ray_ds=True)
+        out = ds.map_batches(pred, batch_size=512, concurrency=1, num_gpus=1).take_all()
+        acc = sum(int(r["predicted_values"] == l) for r, l in zip(out, ds._cols["labels"])) / len(out)
+        assert abs(acc - result.metrics["accuracy"]) < 0.03, (acc, result.metrics["accuracy"])
+        print(f"[mgpu] trainer ok (val_loss {hist['val_loss'].iloc[0]:.4f} -> {hist['val_loss'].iloc[-1]:.4f}, accuracy {acc:.4f})", flush=True)
+    dist.barrier()
 
 
 def main():
@@ -154,13 +205,15 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
-    which = sys.argv[1:] or ["collectives", "ddp", "engine"]
+    which = sys.argv[1:] or ["collectives", "ddp", "engine", "trainer"]
     if "collectives" in which:
         check_collectives(rank, world, dev)
     if "ddp" in which:
         check_ddp(rank, world, dev)
     if "engine" in which:
         check_engine(rank, world, dev)
+    if "trainer" in which:
+        check_trainer(rank, world, dev)
     dist.barrier()
     dist.destroy_process_group()
     if rank == 0:
