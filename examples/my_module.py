@@ -101,8 +101,9 @@ def train_func_per_worker(config: Dict):
 
     print("[my_module] Preparing distributed data loaders...")
     train_loader, val_loader = get_dataloaders(batch_size=batch_size)
-    train_loader = prepare_data_loader(train_loader)
-    val_loader = prepare_data_loader(val_loader)
+    transfer = config.get("input_transfer")          # None: "auto" (dataset resident in HBM when it fits, else streamed)
+    train_loader = prepare_data_loader(train_loader, transfer=transfer)
+    val_loader = prepare_data_loader(val_loader, transfer=transfer)
 
     model = NeuralNetwork()
     start_epoch, val_losses, val_acc, best_val_loss = 0, [], [], float("inf")
@@ -171,11 +172,12 @@ def train_func_per_worker(config: Dict):
 
 def train_fashion_mnist(num_workers=1, use_gpu=False, global_batch_size=32, learning_rate=1e-3, epochs=10,
                         num_checkpoints_to_keep=2, checkpoint_storage_path=None, checkpoint=None, exact_resume=False,
-                        max_failures=0):
+                        max_failures=0, input_transfer=None):
     """Same signature and defaults as the reference's driver (my_ray_module.py:216-251), plus
-    ``exact_resume`` (also restore optimizer state / epoch) and ``max_failures`` (worker-group restarts)."""
+    ``exact_resume`` (also restore optimizer state / epoch), ``max_failures`` (worker-group restarts) and
+    ``input_transfer`` (``prepare_data_loader(transfer=...)``: "resident", "stream" or "host_gather"; default "auto")."""
     train_config = {"lr": learning_rate, "epochs": epochs, "batch_size_per_worker": global_batch_size // num_workers,
-                    "exact_resume": exact_resume}
+                    "exact_resume": exact_resume, "input_transfer": input_transfer}
     if checkpoint is not None:
         train_config["checkpoint"] = checkpoint
     run_config = RunConfig(checkpoint_config=CheckpointConfig(num_to_keep=num_checkpoints_to_keep),

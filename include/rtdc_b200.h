@@ -144,6 +144,7 @@ int rtdc_colsum(const float* x, int ld, int rows, int cols, float* out, void* sc
  *     (use rtdc_colsum with your own scratch for those). rows is unlimited.
  *   - The first call on each device looks the array's address up (cudaGetSymbolAddress, with that
  *     device current) and remembers it; make that first call before starting any stream capture.
+ *   - The scratch used is the CURRENT device's: call it with the device that owns `stream` (and x / out) current.
  *   - No cudaMalloc / cudaFree / allocating library routine is called, on the first call or later.
  *   - All calls on a device share the one array. Each call clears the counters it depends on before
  *     launching, so a call never inherits state from the previous one; but two calls that can run on
@@ -162,6 +163,15 @@ int rtdc_u8_affine(const uint8_t* src, float* dst, size_t n, float scale, float 
 /* Same with the grid capped at `blocks` thread blocks (0 = no cap): a conversion that runs on a side stream next to a
  * tensor-bound kernel is paced down so that it does not fight that kernel for issue slots and L2 bandwidth. */
 int rtdc_u8_affine_paced(const uint8_t* src, float* dst, size_t n, float scale, float shift, int blocks, void* stream);
+
+/* Input batches out of a device-resident uint8 dataset (K9, resident mode): out[r,:] = src[idx[r],:] for r < rows
+ * (row_bytes a multiple of 16, pointers 16-byte aligned), y_out[r] = (int64) labels[idx[r]] when labels is given.
+ * ref: what DataLoader(shuffle=True) + default_collate do on the host (my_ray_module.py:74), done at HBM speed. */
+int rtdc_u8_gather_rows(const uint8_t* src, const int32_t* idx, int rows, int row_bytes, uint8_t* out,
+                        const uint8_t* labels_or_null, int64_t* y_out_or_null, void* stream);
+/* Input batches by the copy engines (K9, streaming mode): n pieces of a PINNED HOST buffer, src_host_base + src_offsets[i],
+ * sizes[i] bytes each (host arrays), are copied back to back into dst_dev with one cudaMemcpyAsync per piece on `stream`. */
+int rtdc_h2d_pieces(void* dst_dev, const void* src_host_base, const int64_t* src_offsets, const int64_t* sizes, int n, void* stream);
 
 /* ReLU(+inverted dropout) backward with padding in one pass: dz[r,c] = dy[r,c] * (y[r,c] > 0 ? scale : 0) for c < cols (y = the
  * layer's output; y NULL copies dy), dz[r,c] = 0 for cols <= c < cols_out. Used for the last layer of a fused chain, whose

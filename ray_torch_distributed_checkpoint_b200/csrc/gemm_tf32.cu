@@ -1092,6 +1092,42 @@ static int num_sms() {
   return n;
 }
 
+// Tuning knobs from the environment, read ONCE when the library first plans a GEMM (not per launch):
+//   RTDC_GEMM_2CTA=0/1        force the 1-CTA / CTA-pair kernel      RTDC_GEMM_2CTA_BK=16   16-wide K blocks for the pair kernel
+//   RTDC_GEMM_SPLITS_LAST=n   K splits of a narrow last N column     RTDC_GEMM_NO_TMA3D     2-D maps for MN-major operands
+//   RTDC_GEMM_NO_TMA_STORE    direct-store epilogue
+// Builds with -DRTDC_GEMM_DEBUG_HOOKS additionally honour RTDC_GEMM_DEBUG (role mask) and RTDC_GEMM_DEBUG_BUF (device pointer of
+// a clock-stamp buffer, used by tools/gemm_stamps*.py); the default build ignores both.
+struct GemmKnobs {
+  int force_2cta = -1;     // -1 unset, 0, 1
+  int bk16 = 0;
+  int splits_last = 0;     // 0 unset
+  int no_tma3d = 0, no_tma_store = 0;
+  int debug = 0;
+  long long* dbg_times = nullptr;
+};
+static GemmKnobs read_knobs() {
+    GemmKnobs r;
+    if (const char* e = getenv("RTDC_GEMM_2CTA")) r.force_2cta = e[0] == '1' ? 1 : (e[0] == '0' ? 0 : -1);
+    if (const char* e = getenv("RTDC_GEMM_2CTA_BK")) r.bk16 = atoi(e) == 16;
+    if (const char* e = getenv("RTDC_GEMM_SPLITS_LAST")) r.splits_last = atoi(e);
+    r.no_tma3d = getenv("RTDC_GEMM_NO_TMA3D") != nullptr;
+    r.no_tma_store = getenv("RTDC_GEMM_NO_TMA_STORE") != nullptr;
+#ifdef RTDC_GEMM_DEBUG_HOOKS
+    if (const char* e = getenv("RTDC_GEMM_DEBUG")) r.debug = atoi(e);
+    if (const char* e = getenv("RTDC_GEMM_DEBUG_BUF")) r.dbg_times = reinterpret_cast<long long*>(strtoull(e, nullptr, 0));
+#endif
+    return r;
+}
+#ifdef RTDC_GEMM_DEBUG_HOOKS
+static GemmKnobs knobs() { return read_knobs(); }                 // probe tools flip the variables between launches
+#else
+static const GemmKnobs& knobs() {
+  static const GemmKnobs k = read_knobs();
+  return k;
+}
+#endif
+
 static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
   if (!d) return fail(RTDC_ERR_ARG, "null descriptor");
   if (d->M <= 0 || d->N <= 0 || d->K <= 0) return fail(RTDC_ERR_ARG, "M, N, K must be positive (got %d, %d, %d)", d->M, d->N, d->K);
@@ -1099,16 +1135,16 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
   // CTA pairs (cta_group::2) for the fp32-accurate path: a pair shares one 256-row tile, each CTA stages half of B, so
   // shared-memory traffic per SM drops by a third and the main loop becomes tensor-bound. Used when the tile grid pairs up
   // and the coarser N granularity does not cost more padding than it saves. RTDC_GEMM_2CTA=0/1 forces the choice.
-  const char* env2 = getenv("RTDC_GEMM_2CTA");
+  const GemmKnobs kn = knobs();
   const int gran2 = d->b_mn ? 64 : 32, gran1 = d->b_mn ? 32 : 16;
   bool two_cta = d->precision == 3 && d->M > BM && d->N >= 128;
   if (two_cta && d->bn != 0 && d->bn % gran2 != 0) two_cta = false;
-  if (two_cta && d->bn == 0 && !(env2 && env2[0] == '1')) {
+  if (two_cta && d->bn == 0 && kn.force_2cta != 1) {
     const int nt = ceil_div(d->N, MAX_BN);
     const int bn1 = round_up(ceil_div(d->N, nt), (nt > 1 && gran1 < 32) ? 32 : gran1), bn2 = round_up(ceil_div(d->N, nt), gran2);
     if (ceil_div(d->N, bn2) * bn2 * 100 > ceil_div(d->N, bn1) * bn1 * 120) two_cta = false;
   }
-  if (env2 && env2[0] == '0') two_cta = false;
+  if (kn.force_2cta == 0) two_cta = false;
   pl->two_cta = two_cta ? 1 : 0;
   const int gran = two_cta ? (d->b_mn ? 64 : 32) : (d->b_mn ? 32 : 16);
   int bn = d->bn;
@@ -1127,8 +1163,7 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
     return fail(RTDC_ERR_ARG, "n_store (%d) reaches beyond the last N tile", d->n_store);
   // K block: the 1-CTA 3xTF32 kernel needs 16 to fit four stages of raw + tail tiles; a CTA pair stages half of B, so 32
   // fits three (and halves the per-stage barrier / commit overhead of the issuer thread). RTDC_GEMM_2CTA_BK=16 forces 16.
-  const char* envbk = getenv("RTDC_GEMM_2CTA_BK");
-  pl->bk = d->precision == 3 ? ((two_cta && !(envbk && atoi(envbk) == 16)) ? 32 : 16) : 32;
+  pl->bk = d->precision == 3 ? ((two_cta && !kn.bk16) ? 32 : 16) : 32;
   pl->num_kb = ceil_div(d->K, pl->bk);
   pl->a_bytes = BM * pl->bk * 4;
   pl->b_bytes = static_cast<uint32_t>(two_cta ? bn / 2 : bn) * pl->bk * 4;   // a CTA of a pair stages half of B
@@ -1171,7 +1206,6 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
     const int slots = sms / m_sched, nt = pl->n_tiles;
     int cap = d->K / 256 < 64 ? d->K / 256 : 64;
     if (cap < 1) cap = 1;
-    const char* envl = getenv("RTDC_GEMM_SPLITS_LAST");
     if (w_last < bn && slots >= nt) {
       const double c_full = 1.0, c_last = 0.75 + 0.25 * static_cast<double>(w_last) / bn;   // measured: a 64-wide unit costs ~80 % of a 256-wide one per K block
       double best = 1e30;
@@ -1180,7 +1214,7 @@ static int make_plan(const rtdc_gemm_desc* d, Plan* pl, bool need_device) {
         int sf = (slots - sl) / (nt - 1);
         if (sf > cap) sf = cap;
         if (sf < sl) continue;                       // partial slots are laid out with stride splits_full
-        if (envl && atoi(envl) != sl) continue;
+        if (kn.splits_last && kn.splits_last != sl) continue;
         const double cost_f = ceil_div(pl->num_kb, sf) * c_full, cost_l = ceil_div(pl->num_kb, sl) * c_last;
         const double cost = cost_f > cost_l ? cost_f : cost_l;
         if (cost <= best + 1e-9) { best = cost; best_f = sf; best_l = sl; }   // ties: more splits for the last column
@@ -1279,7 +1313,7 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   // one-instruction loads of MN-major tiles over the whole 32-element blocks of the operand (RTDC_GEMM_NO_TMA3D=1: off)
   CUtensorMap ta3, tb3;
   memset(&ta3, 0, sizeof(ta3)); memset(&tb3, 0, sizeof(tb3));
-  const bool use3 = !getenv("RTDC_GEMM_NO_TMA3D");
+  const bool use3 = !knobs().no_tma3d;
   if (use3 && d->a_mn && d->M >= BM) {
     rc = make_map3_mn(&ta3, d->a, d->M / 32, d->K, d->lda, pl.bk, BM / 32);
     if (rc != RTDC_OK) return rc;
@@ -1343,7 +1377,7 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   CUtensorMap to;
   memset(&to, 0, sizeof(to));
   if ((reinterpret_cast<uintptr_t>(d->out) & 15u) == 0 && (static_cast<size_t>(d->ldo) * 4) % 16 == 0 &&
-      (pl.bn % 32 == 0 || pl.n_tiles == 1) && !getenv("RTDC_GEMM_NO_TMA_STORE")) {
+      (pl.bn % 32 == 0 || pl.n_tiles == 1) && !knobs().no_tma_store) {
     rc = make_map(&to, d->out, n_store, d->M, d->ldo, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != RTDC_OK) return rc;
     gp.tma_store = 1;
@@ -1353,8 +1387,8 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
     if (d->ld_colsum < d->N) return fail(RTDC_ERR_ARG, "ld_colsum (%d) smaller than N (%d)", d->ld_colsum, d->N);
     gp.colsum_partial = d->colsum_partial; gp.ld_colsum = d->ld_colsum;
   }
-  if (const char* dbg = getenv("RTDC_GEMM_DEBUG")) gp.debug = atoi(dbg);
-  if (const char* dbg = getenv("RTDC_GEMM_DEBUG_BUF")) gp.dbg_times = reinterpret_cast<long long*>(strtoull(dbg, nullptr, 0));
+  gp.debug = knobs().debug;             // both stay 0 / null unless built with -DRTDC_GEMM_DEBUG_HOOKS
+  gp.dbg_times = knobs().dbg_times;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool three = d->precision == 3;
   rc = dispatch(d, three, ta, tb, to, ta3, tb3, gp, pl, st);

@@ -267,66 +267,210 @@ def dump_timing(rank: int):
     os.replace(tmp, f"{path}.{rank}")
 
 
+class BlockSampler:
+    """Two-level shuffle for the streaming transfer: the epoch's order is a permutation of BLOCKS of ``block`` consecutive
+    rows (of a dataset that was row-shuffled once when the loader was built), sharded over ranks like
+    ``DistributedSampler`` shards rows: the block list is padded to a multiple of the world size by wrapping around and rank
+    r takes every world-th block. Every block has exactly ``block`` rows (the last one is ``[N - block, N)``, i.e. it
+    overlaps its neighbour instead of being short), so all ranks see the same number of rows. A batch is then a run of
+    contiguous row ranges — something copy engines move without any host-side gather."""
+
+    def __init__(self, dataset_len: int, block: int, num_replicas: int, rank: int, shuffle: bool = True, seed: int = 0):
+        self.n = int(dataset_len)
+        self.block = max(1, min(int(block), self.n))
+        self.num_replicas, self.rank, self.shuffle, self.seed, self.epoch = num_replicas, rank, shuffle, seed, 0
+        self.nblocks = math.ceil(self.n / self.block)
+        self.blocks_per_rank = math.ceil(self.nblocks / num_replicas)
+
+    def set_epoch(self, epoch: int) -> None:
+        self.epoch = int(epoch)
+
+    def block_starts(self) -> list:
+        """First row of each block of this rank's shard for the current epoch."""
+        if self.shuffle:
+            g = torch.Generator()
+            g.manual_seed(self.seed + self.epoch)
+            order = torch.randperm(self.nblocks, generator=g).tolist()
+        else:
+            order = list(range(self.nblocks))
+        total = self.blocks_per_rank * self.num_replicas
+        pad = total - len(order)
+        if pad > 0:
+            order += (order * math.ceil(pad / len(order)))[:pad]
+        mine = order[self.rank:total:self.num_replicas]
+        last = self.n - self.block
+        return [min(b * self.block, last) for b in mine]
+
+    def __len__(self) -> int:
+        return self.blocks_per_rank * self.block
+
+    def __iter__(self):
+        for s in self.block_starts():
+            yield from range(s, s + self.block)
+
+
+def shared_pinned_rows(rows: torch.Tensor, order: Optional[torch.Tensor], world: int, rank: int) -> torch.Tensor:
+    """``rows[order]`` (or ``rows``) as ONE page-locked host buffer per node, mapped by every rank, instead of one private
+    pinned copy per rank: the node's first rank writes it into a POSIX shared-memory file, every rank maps that file and
+    registers the mapping with the CUDA driver (``cudaHostRegister``), after which copy engines of all GPUs read the same
+    physical pages. Collective over the default process group when ``world > 1``; a private pinned tensor otherwise."""
+    import torch.distributed as dist
+    n, row = rows.shape
+    if world <= 1 or not (dist.is_available() and dist.is_initialized() and dist.get_world_size() == world):
+        out = torch.empty(n, row, dtype=rows.dtype, pin_memory=True)
+        if order is not None:
+            torch.index_select(rows, 0, order, out=out)
+        else:
+            out.copy_(rows)
+        return out
+    import os
+    import uuid
+    box = [f"/dev/shm/rtdc_ds_{os.getpid()}_{uuid.uuid4().hex[:8]}" if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    path, nbytes = box[0], n * row * rows.element_size()
+    if rank == 0:
+        flat = torch.from_file(path, shared=True, size=nbytes, dtype=torch.uint8)
+        view = flat.view(rows.dtype).view(n, row)
+        if order is not None:
+            torch.index_select(rows, 0, order, out=view)
+        else:
+            view.copy_(rows)
+    dist.barrier()
+    if rank != 0:
+        flat = torch.from_file(path, shared=True, size=nbytes, dtype=torch.uint8)
+        view = flat.view(rows.dtype).view(n, row)
+    rc = torch.cuda.cudart().cudaHostRegister(flat.data_ptr(), nbytes, 0)
+    if int(rc) != 0:
+        raise RuntimeError(f"cudaHostRegister of the shared dataset failed with code {int(rc)}")
+    dist.barrier()
+    if rank == 0:
+        os.unlink(path)                      # the mappings keep the pages alive
+    return view
+
+
+_live_loaders = None
+
+
+def _register_for_exit(loader):
+    """Background shuffle threads must not be inside torch's thread pool when the interpreter tears down."""
+    global _live_loaders
+    if _live_loaders is None:
+        import atexit
+        import weakref
+        _live_loaders = weakref.WeakSet()
+
+        def _join_all():
+            for ld in list(_live_loaders):
+                ld.close()
+        atexit.register(_join_all)
+    _live_loaders.add(loader)
+
+
 class U8BatchLoader:
-    """Epoch iterator over a uint8 image set held in host memory, built for PCIe + HBM rather than for
-    a Python collate loop.
+    """Epoch iterator over a uint8 image set, built for PCIe + HBM rather than for a Python collate loop. Pixels and
+    labels travel as bytes (4x fewer pixel bytes than the reference's float32 batches, 8x fewer label bytes than int64;
+    my_ray_module.py:38,128), batches are assembled ``lookahead`` steps ahead of the consumer on a side stream into a ring
+    of device buffers, and normalisation (ToTensor + Normalize) happens on the GPU. Three ways to get a shuffled batch onto
+    the device (``transfer``):
 
-    * The shuffle is done once per epoch, off the critical path: a background thread gathers this
-      rank's shard of the epoch's permutation into a pinned buffer (``index_select`` on all host cores)
-      while the previous epoch is still training (two pinned buffers, ping-pong).
-    * Every step is then ONE contiguous ``cudaMemcpyAsync`` of uint8 pixels plus one of uint8 labels on a
-      copy stream — 4x fewer pixel bytes than the reference's float32 batches and 8x fewer label bytes than int64
-      (my_ray_module.py:38, 128) — issued ``lookahead`` steps ahead of the consumer, into a ring of device buffers;
-      labels are widened to int64 on the device.
-    * Normalisation (ToTensor + Normalize) happens on the GPU: the consumer takes the uint8 batch (the fused
-      engine normalises inside its graph); with ``wrap=True`` batches are :class:`U8Images` (image-shaped, normalise
-      themselves on first generic use); with ``normalize=True`` this loader runs ``ops.u8_normalize`` and yields float32.
+    * ``"resident"`` — the dataset is uploaded ONCE and stays in HBM (all of FashionMNIST is 47 MB of a 180 GB device).
+      Per epoch the sampler's permutation (``DistributedSampler`` arithmetic, exact row-level shuffle) is uploaded as
+      int32 indices; per step ``ops.u8_gather_rows`` assembles the batch at HBM speed. ``"auto"`` picks this whenever the
+      dataset fits ``resident_max_bytes``.
+    * ``"stream"`` — the dataset stays in pinned host memory and every step's pixels cross PCIe by DMA. To need no
+      host-side gather the shuffle has two levels (:class:`BlockSampler`): rows are shuffled once when the loader is
+      built, and each epoch permutes and shards blocks of ``shuffle_block`` consecutive rows; a batch is ~B/shuffle_block
+      contiguous pieces, one ``cudaMemcpyAsync`` each (``ops.h2d_pieces``).
+    * ``"host_gather"`` — exact row-level shuffle with the dataset on the host: a background thread gathers the rank's
+      shard of the epoch's permutation into a pinned buffer (``index_select``; ping-pong with the next epoch), each step is
+      one contiguous copy. Exact and simple, but a host gathers 784-byte rows at a few GB/s: at B200 step times it
+      is the slowest of the three by far.
 
-    Yields ``(x, labels)`` on the device; ``x`` is ``uint8 [B, features]``, ``U8Images [B, *image_shape]`` or
-    ``float32 [B, features]``; ``labels`` is ``int64 [B]``.
+    Yields ``(x, labels)`` on the device; ``x`` is ``uint8 [B, features]``, :class:`U8Images` ``[B, *image_shape]``
+    (``wrap=True``) or ``float32 [B, features]`` (``normalize=True``); ``labels`` is ``int64 [B]``.
     """
 
     def __init__(self, images_u8: torch.Tensor, labels: torch.Tensor, batch_size: int, device, *, shuffle: bool = True,
                  world: int = 1, rank: int = 0, seed: int = 0, drop_last: bool = True, normalize: bool = False,
                  mean: float = 0.5, std: float = 0.5, lookahead: int = 2, prefetch_next_epoch: bool = True,
-                 wrap: bool = False, timed: bool = False):
+                 wrap: bool = False, timed: bool = False, transfer: str = "auto", shuffle_block: int = 512,
+                 resident_max_bytes: int = 4 << 30):
         assert images_u8.dtype == torch.uint8 and labels.dtype in (torch.int64, torch.uint8)
         self.prefetch_next_epoch = prefetch_next_epoch
         self.image_shape = tuple(images_u8.shape[1:]) if images_u8.dim() > 2 else (images_u8.shape[1],)
         if len(self.image_shape) == 2:
             self.image_shape = (1,) + self.image_shape          # ToTensor's channel dimension
-        self.images = images_u8.reshape(images_u8.shape[0], -1).contiguous()
-        # labels cross PCIe as bytes when they fit (10 classes do)
+        images = images_u8.reshape(images_u8.shape[0], -1)
+        # labels travel as bytes when they fit (10 classes do)
         self.label_dtype = torch.uint8 if (labels.dtype == torch.uint8 or (labels.numel() and 0 <= int(labels.min()) and int(labels.max()) < 256)) else torch.int64
-        self.labels = labels.to(self.label_dtype).contiguous()
-        self.row = self.images.shape[1]
+        labels = labels.to(self.label_dtype)
+        self.row = images.shape[1]
         self.batch_size = int(batch_size)
         self.device = torch.device(device)
-        self.sampler = DistributedSampler(self.images.shape[0], world, rank, shuffle=shuffle, seed=seed)
+        self.cuda = self.device.type == "cuda"
+        n_rows = images.shape[0]
+        if transfer not in ("auto", "resident", "stream", "host_gather"):
+            raise ValueError(f"transfer must be 'auto', 'resident', 'stream' or 'host_gather' (got {transfer!r})")
+        if not self.cuda:
+            transfer = "host_gather"
+        elif transfer in ("auto", "resident"):
+            fits = n_rows * (self.row + 1) <= resident_max_bytes and self.row % 16 == 0 and self.label_dtype == torch.uint8
+            if transfer == "resident" and not fits:
+                raise ValueError("transfer='resident' needs uint8 labels, a row length that is a multiple of 16 bytes and a dataset within resident_max_bytes")
+            transfer = "resident" if fits else "stream"
+        self.transfer = transfer
         self.drop_last = drop_last
         self.normalize, self.mean, self.std = normalize, mean, std
         self.wrap, self.timed = wrap, timed
-        self.cuda = self.device.type == "cuda"
         self.lookahead = max(1, int(lookahead))
-        n = len(self.sampler)
-        self._host_x = [torch.empty(n, self.row, dtype=torch.uint8, pin_memory=self.cuda) for _ in range(2)]
-        self._host_y = [torch.empty(n, dtype=self.label_dtype, pin_memory=self.cuda) for _ in range(2)]
-        self._prepared = {}          # epoch -> (slot, thread)
-        self._epoch_iter = 0
+        self._prepared = {}          # host_gather: epoch -> (slot, thread)
+        self._closed = False
+
+        if transfer == "stream":
+            self.sampler = BlockSampler(n_rows, shuffle_block, world, rank, shuffle=shuffle, seed=seed)
+            if shuffle:                                      # level one: rows, once
+                g = torch.Generator()
+                g.manual_seed(seed + 0x5EED)
+                order = torch.randperm(n_rows, generator=g)
+                self.images = shared_pinned_rows(images, order, world, rank)
+                self.labels = torch.index_select(labels, 0, order).contiguous()
+            else:
+                self.images = images.contiguous() if images.is_pinned() else shared_pinned_rows(images, None, world, rank)
+                self.labels = labels.contiguous()
+            n = len(self.sampler)
+            self._host_y = [torch.empty(n, dtype=self.label_dtype, pin_memory=True) for _ in range(2)]
+            self.h2d_bytes_per_batch = self.batch_size * (self.row + (1 if self.label_dtype == torch.uint8 else 8))
+        else:
+            self.sampler = DistributedSampler(n_rows, world, rank, shuffle=shuffle, seed=seed)
+            n = len(self.sampler)
+            if transfer == "resident":
+                self.images = images.contiguous().to(self.device)            # the one upload of the pixels
+                self.labels = labels.contiguous().to(self.device)
+                self._host_idx = [torch.empty(n, dtype=torch.int32, pin_memory=True) for _ in range(2)]
+                self._dev_idx = [torch.empty(n, dtype=torch.int32, device=self.device) for _ in range(2)]
+                self.h2d_bytes_per_batch = self.batch_size * 4                # the batch's indices
+            else:
+                self.images = images.contiguous()
+                self.labels = labels.contiguous()
+                self._host_x = [torch.empty(n, self.row, dtype=torch.uint8, pin_memory=self.cuda) for _ in range(2)]
+                self._host_y = [torch.empty(n, dtype=self.label_dtype, pin_memory=self.cuda) for _ in range(2)]
+                self.h2d_bytes_per_batch = self.batch_size * (self.row + (1 if self.label_dtype == torch.uint8 else 8))
         if self.cuda:
             ring = self.lookahead + 2
             self._dev_x = [torch.empty(self.batch_size, self.row, dtype=torch.uint8, device=self.device) for _ in range(ring)]
             self._dev_y = [torch.empty(self.batch_size, dtype=torch.int64, device=self.device) for _ in range(ring)]
             self._dev_y8 = ([torch.empty(self.batch_size, dtype=torch.uint8, device=self.device) for _ in range(ring)]
-                            if self.label_dtype == torch.uint8 else None)
+                            if (self.label_dtype == torch.uint8 and transfer != "resident") else None)
             self._dev_f = ([torch.empty(self.batch_size, self.row, dtype=torch.float32, device=self.device) for _ in range(ring)]
                            if normalize else None)
             self._free_ev = [None] * ring
             self.copy_stream = torch.cuda.Stream(self.device)
-        self.h2d_bytes_per_batch = self.batch_size * (self.row + (1 if self.label_dtype == torch.uint8 else 8))
         if timed:
             TIMING["extra"]["h2d_bytes_per_step"] = self.h2d_bytes_per_batch
-        self._prepare(self.sampler.epoch)
+            TIMING["extra"]["input_transfer"] = transfer
+        if transfer == "host_gather":
+            _register_for_exit(self)
+            self._prepare(self.sampler.epoch)
 
     @property
     def dataset(self):
@@ -336,9 +480,15 @@ class U8BatchLoader:
         n = len(self.sampler)
         return n // self.batch_size if self.drop_last else math.ceil(n / self.batch_size)
 
-    # ---------------------------------------------------------------- epoch permutation (background)
+    def close(self):
+        """Join the background shuffle threads (host_gather)."""
+        self._closed = True
+        for e in list(self._prepared):
+            self._prepared.pop(e)[1].join()
+
+    # ---------------------------------------------------------------- host_gather: epoch permutation (background)
     def _prepare(self, epoch: int):
-        if epoch in self._prepared:
+        if epoch in self._prepared or self._closed:
             return
         slot = epoch % 2
         old_epoch = self.sampler.epoch
@@ -354,15 +504,15 @@ class U8BatchLoader:
         th.start()
         self._prepared[epoch] = (slot, th)
 
-    def _emit(self, xb: torch.Tensor, yb: torch.Tensor):
-        if self.normalize:
+    def _emit(self, xb: torch.Tensor, yb: torch.Tensor, ready=None):
+        if self.normalize or not self.wrap:
             return xb, yb
-        if self.wrap:
-            return U8Images.wrap(xb.view(xb.shape[0], *self.image_shape), self.mean, self.std), yb
-        return xb, yb
+        x = U8Images.wrap(xb.view(xb.shape[0], *self.image_shape), self.mean, self.std)
+        x._ready = ready              # the event after which these bytes (and the labels) are in place
+        return x, yb
 
-    def __iter__(self):
-        epoch = self.sampler.epoch
+    # ---------------------------------------------------------------- per-epoch set-up of each transfer
+    def _epoch_host_gather(self, epoch: int):
         self._prepare(epoch)
         slot, th = self._prepared.pop(epoch)
         th.join()
@@ -370,11 +520,61 @@ class U8BatchLoader:
             if e != epoch + 1:
                 self._prepared.pop(e)[1].join()
         hx, hy = self._host_x[slot], self._host_y[slot]
+        if len(self) > 1 and self.prefetch_next_epoch:
+            self._prepare(epoch + 1)            # next epoch's shuffle overlaps this epoch's training
+
+        def fill(bi, lo, hi):
+            self._dev_x[bi][:hi - lo].copy_(hx[lo:hi], non_blocking=True)
+            self._copy_labels(bi, hy, lo, hi)
+        return fill, (hx, hy)
+
+    def _copy_labels(self, bi, hy, lo, hi):
+        if self._dev_y8 is not None:
+            self._dev_y8[bi][:hi - lo].copy_(hy[lo:hi], non_blocking=True)
+            self._dev_y[bi][:hi - lo].copy_(self._dev_y8[bi][:hi - lo])        # widen on the device
+        else:
+            self._dev_y[bi][:hi - lo].copy_(hy[lo:hi], non_blocking=True)
+
+    def _epoch_resident(self, epoch: int):
+        from ..ops import u8_gather_rows
+        slot = epoch % 2
+        self._host_idx[slot].copy_(torch.as_tensor(self.sampler.indices(), dtype=torch.int32))
+        with torch.cuda.stream(self.copy_stream):
+            self._dev_idx[slot].copy_(self._host_idx[slot], non_blocking=True)
+        idx = self._dev_idx[slot]
+
+        def fill(bi, lo, hi):
+            u8_gather_rows(self.images, idx[lo:hi], self._dev_x[bi], labels=self.labels, y_out=self._dev_y[bi], stream=self.copy_stream)
+        return fill, None
+
+    def _epoch_stream(self, epoch: int):
+        from ..ops import h2d_pieces
+        slot = epoch % 2
+        starts = torch.as_tensor(self.sampler.block_starts(), dtype=torch.int64)
+        G = self.sampler.block
+        hy = self._host_y[slot]
+        # this epoch's labels in shard order: a few hundred KB, gathered here once; the pixels are never gathered on the host
+        torch.index_select(self.labels.view(-1), 0, (starts[:, None] + torch.arange(G)[None, :]).reshape(-1), out=hy)
+        row = self.row
+
+        def fill(bi, lo, hi):
+            b0, b1 = lo // G, (hi - 1) // G
+            offs = starts[b0:b1 + 1] * row
+            sizes = torch.full((b1 - b0 + 1,), G * row, dtype=torch.int64)
+            head = lo - b0 * G                                   # the window may start / end inside a block
+            offs[0] += head * row
+            sizes[0] -= head * row
+            sizes[-1] -= ((b1 + 1) * G - hi) * row
+            h2d_pieces(self._dev_x[bi], self.images, offs, sizes, stream=self.copy_stream)
+            self._copy_labels(bi, hy, lo, hi)
+        return fill, None
+
+    def __iter__(self):
+        epoch = self.sampler.epoch
         nb, bs = len(self), self.batch_size
         total = len(self.sampler)
-        if nb > 1 and self.prefetch_next_epoch:
-            self._prepare(epoch + 1)            # next epoch's shuffle overlaps this epoch's training
         if not self.cuda:
+            _, (hx, hy) = self._epoch_host_gather(epoch)
             for i in range(nb):
                 x = hx[i * bs:min(total, (i + 1) * bs)]
                 y = hy[i * bs:min(total, (i + 1) * bs)].to(torch.int64)
@@ -388,8 +588,9 @@ class U8BatchLoader:
                 if self.timed:
                     _stamp("step_end", self.device)
             return
+        fill, _ = {"host_gather": self._epoch_host_gather, "resident": self._epoch_resident, "stream": self._epoch_stream}[self.transfer](epoch)
         ring = len(self._dev_x)
-        inflight = []                            # (buffer index, rows, copy-done event)
+        inflight = []                            # (buffer index, rows, batch-ready event)
         issued = 0
 
         def issue():
@@ -400,12 +601,7 @@ class U8BatchLoader:
             if self._free_ev[bi] is not None:
                 self.copy_stream.wait_event(self._free_ev[bi])      # consumer is done with this device buffer
             with torch.cuda.stream(self.copy_stream):
-                self._dev_x[bi][:hi - lo].copy_(hx[lo:hi], non_blocking=True)
-                if self._dev_y8 is not None:
-                    self._dev_y8[bi][:hi - lo].copy_(hy[lo:hi], non_blocking=True)
-                    self._dev_y[bi][:hi - lo].copy_(self._dev_y8[bi][:hi - lo])        # widen on the device
-                else:
-                    self._dev_y[bi][:hi - lo].copy_(hy[lo:hi], non_blocking=True)
+                fill(bi, lo, hi)
                 ev = torch.cuda.Event()
                 ev.record(self.copy_stream)
             inflight.append((bi, hi - lo, ev))
@@ -425,11 +621,11 @@ class U8BatchLoader:
                 xb = u8_normalize(xb, mean=self.mean, std=self.std, out=self._dev_f[bi][:rows])
             if self.timed:
                 _stamp("step_begin", self.device)
-            yield self._emit(xb, self._dev_y[bi][:rows])
+            yield self._emit(xb, self._dev_y[bi][:rows], ready=ev)
             if self.timed:
                 _stamp("step_end", self.device)
             done = torch.cuda.Event()
             done.record(torch.cuda.current_stream(self.device))
             self._free_ev[bi] = done
-        # the pinned epoch buffer may be rewritten (epoch + 2) only after its last H2D has finished
+        # pinned per-epoch buffers may be rewritten (epoch + 2) only after their last H2D has finished
         self.copy_stream.synchronize()

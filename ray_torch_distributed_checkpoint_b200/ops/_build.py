@@ -29,6 +29,11 @@ NVCC_FLAGS = [
 ]
 
 
+def _flags():
+    """NVCC_FLAGS plus ``$RTDC_EXTRA_NVCC_FLAGS`` (e.g. ``-DRTDC_GEMM_DEBUG_HOOKS`` for the tools/gemm_*probe*.py scripts)."""
+    return NVCC_FLAGS + os.environ.get("RTDC_EXTRA_NVCC_FLAGS", "").split()
+
+
 def _nvcc() -> str:
     for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
         if cand and Path(cand).exists():
@@ -49,7 +54,7 @@ def _digest() -> str:
         if f.is_file():
             h.update(f.name.encode())
             h.update(f.read_bytes())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update(" ".join(_flags()).encode())
     return h.hexdigest()
 
 
@@ -67,36 +72,67 @@ def _run(cmd, verbose):
 
 
 def build(force: bool = False, verbose: bool = False, ptxas_info: bool = False) -> Path:
-    """Compile every translation unit under csrc/ for sm_100a and link the shared library."""
+    """Compile every translation unit under csrc/ for sm_100a and link the shared library.
+
+    Safe to call from many processes at once (every worker rank of a ``TorchTrainer.fit()`` calls it through the first
+    op): an exclusive file lock serialises the check-and-build, objects and the library are produced in a private
+    temporary directory and moved into place with ``os.replace``, so no process can ever map a half-written file."""
     if not force and is_current():
         return LIB_PATH
-    nvcc = _nvcc()
+    import fcntl
+    import tempfile
     LIB_DIR.mkdir(exist_ok=True)
+    with open(LIB_DIR / ".build.lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and is_current():          # somebody else built it while we waited
+                return LIB_PATH
+            return _build_locked(verbose, ptxas_info, Path(tempfile.mkdtemp(prefix=".build_", dir=LIB_DIR)))
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose: bool, ptxas_info: bool, tmp: Path) -> Path:
+    nvcc = _nvcc()
     obj_dir = LIB_DIR / "obj"
     obj_dir.mkdir(exist_ok=True)
     srcs = _sources()
     extra = ["-Xptxas", "-v"] if ptxas_info else []
+    digest = _digest()
 
     def compile_one(src: Path):
-        obj = obj_dir / (src.stem + ".o")
-        log = _run([nvcc, *NVCC_FLAGS, *extra, "-I", str(PKG_DIR.parent / "include"), "-c", str(src), "-o", str(obj)], verbose)
+        obj = tmp / (src.stem + ".o")
+        log = _run([nvcc, *_flags(), *extra, "-I", str(PKG_DIR.parent / "include"), "-c", str(src), "-o", str(obj)], verbose)
         return obj, log
 
-    logs = {}
-    with _fut.ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
-        objs = []
-        for (obj, log), src in zip(ex.map(compile_one, srcs), srcs):
-            objs.append(obj)
-            logs[src.name] = log
-    _run([nvcc, "-shared", "-o", str(LIB_PATH), *map(str, objs), "-lcudart_static", "-ldl", "-lrt", "-lpthread"], verbose)
-    # native worker-group launcher (plain C++ executable, no CUDA)
-    main_cpp = CSRC / "launcher_main.cpp"
-    if main_cpp.exists():
-        cxx = shutil.which("g++") or "g++"
-        _run([cxx, "-O2", "-std=c++17", "-Wall", "-o", str(LAUNCHER_PATH), str(main_cpp), "-lpthread"], verbose)
-    STAMP.write_text(_digest())
-    if ptxas_info:
-        (LIB_DIR / "ptxas_info.txt").write_text("\n".join(f"==== {k}\n{v}" for k, v in logs.items()))
+    try:
+        logs = {}
+        with _fut.ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
+            objs = []
+            for (obj, log), src in zip(ex.map(compile_one, srcs), srcs):
+                objs.append(obj)
+                logs[src.name] = log
+        so = tmp / LIB_PATH.name
+        _run([nvcc, "-shared", "-o", str(so), *map(str, objs), "-lcudart_static", "-ldl", "-lrt", "-lpthread"], verbose)
+        # native worker-group launcher (plain C++ executable, no CUDA)
+        main_cpp = CSRC / "launcher_main.cpp"
+        launcher = None
+        if main_cpp.exists():
+            cxx = shutil.which("g++") or "g++"
+            launcher = tmp / LAUNCHER_PATH.name
+            _run([cxx, "-O2", "-std=c++17", "-Wall", "-o", str(launcher), str(main_cpp), "-lpthread"], verbose)
+        for obj in objs:                             # kept next to the library for cuobjdump / incremental inspection
+            os.replace(obj, obj_dir / obj.name)
+        if launcher is not None:
+            os.replace(launcher, LAUNCHER_PATH)
+        os.replace(so, LIB_PATH)
+        stamp_tmp = tmp / "stamp"
+        stamp_tmp.write_text(digest)
+        os.replace(stamp_tmp, STAMP)                 # last: a reader that sees the stamp sees the finished library
+        if ptxas_info:
+            (LIB_DIR / "ptxas_info.txt").write_text("\n".join(f"==== {k}\n{v}" for k, v in logs.items()))
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
     return LIB_PATH
 
 

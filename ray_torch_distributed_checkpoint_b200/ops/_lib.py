@@ -83,6 +83,10 @@ def _declare(lib):
     lib.rtdc_u8_affine_paced.argtypes = [vp, vp, sz, f, f, i, vp]
     lib.rtdc_u8_affine_paced.restype = i
     lib.rtdc_fold_input_bias.argtypes = [vp, i, i, i, vp, f, vp, vp]
+    lib.rtdc_u8_gather_rows.argtypes = [vp, vp, i, i, vp, vp, vp, vp]
+    lib.rtdc_u8_gather_rows.restype = i
+    lib.rtdc_h2d_pieces.argtypes = [vp, vp, vp, vp, i, vp]
+    lib.rtdc_h2d_pieces.restype = i
     lib.rtdc_act_backward.argtypes = [vp, i, vp, i, i, i, i, f, vp, i, vp]
     lib.rtdc_act_backward.restype = i
     lib.rtdc_sgd_step.argtypes = [vp, vp, vp, sz, vp, vp]

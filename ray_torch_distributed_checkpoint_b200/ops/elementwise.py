@@ -109,6 +109,34 @@ def act_backward(dy: torch.Tensor, y: Optional[torch.Tensor], *, scale: float = 
     return out
 
 
+def u8_gather_rows(src: torch.Tensor, idx: torch.Tensor, out: torch.Tensor, *, labels: Optional[torch.Tensor] = None,
+                   y_out: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
+    """``out[r] = src[idx[r]]`` over a device-resident uint8 matrix (row length a multiple of 16 bytes), and
+    ``y_out[r] = labels[idx[r]]`` widened to int64: a shuffled batch assembled at HBM speed."""
+    if src.dtype != torch.uint8 or out.dtype != torch.uint8 or idx.dtype != torch.int32 or not (src.is_cuda and out.is_cuda and idx.is_cuda):
+        raise ValueError("src/out must be uint8 and idx int32 CUDA tensors")
+    rows = idx.numel()
+    if out.shape[0] < rows or not (src.is_contiguous() and out.is_contiguous() and idx.is_contiguous()):
+        raise ValueError("out too small or tensors not contiguous")
+    if labels is not None and (labels.dtype != torch.uint8 or y_out is None or y_out.dtype != torch.int64 or y_out.numel() < rows):
+        raise ValueError("labels must be uint8 with an int64 y_out of at least idx.numel() elements")
+    _lib.check(_lib.load().rtdc_u8_gather_rows(src.data_ptr(), idx.data_ptr(), rows, src.shape[1], out.data_ptr(),
+                                               labels.data_ptr() if labels is not None else None,
+                                               y_out.data_ptr() if labels is not None else None, _lib.stream_ptr(stream)))
+    return out
+
+
+def h2d_pieces(dst: torch.Tensor, src_host: torch.Tensor, offsets: torch.Tensor, sizes: torch.Tensor, stream=None) -> None:
+    """Copy pieces of the pinned host tensor ``src_host`` (byte ``offsets`` / ``sizes``: int64 CPU tensors) back to back into the
+    device tensor ``dst`` with one ``cudaMemcpyAsync`` each, issued from native code."""
+    if not src_host.is_pinned() or not dst.is_cuda or offsets.dtype != torch.int64 or sizes.dtype != torch.int64 or offsets.is_cuda:
+        raise ValueError("src_host must be pinned, dst on the device, offsets/sizes int64 CPU tensors")
+    if int(sizes.sum()) > dst.numel() * dst.element_size():
+        raise ValueError("pieces do not fit the destination")
+    _lib.check(_lib.load().rtdc_h2d_pieces(dst.data_ptr(), src_host.data_ptr(), offsets.data_ptr(), sizes.data_ptr(), offsets.numel(),
+                                           _lib.stream_ptr(stream)))
+
+
 def u8_normalize(src: torch.Tensor, *, mean: float = 0.5, std: float = 0.5, out: Optional[torch.Tensor] = None,
                  stream=None) -> torch.Tensor:
     """uint8 pixels -> float32 ``(x/255 - mean)/std``, any shape (contiguous)."""

@@ -18,18 +18,27 @@ PRECISION_FP32 = 3   # 3xTF32, fp32-equivalent accuracy (default: the reference 
 PRECISION_TF32 = 1
 
 _scratch = {}
+_retired = []      # outgrown workspaces: never freed, captured CUDA graphs may still hold their addresses
 
 
 def scratch_for(tag: str, nbytes: int, device, stream=None) -> torch.Tensor:
     """Zero-initialised per-(device, stream, tag) workspace that only ever grows.
 
     Kernels leave their arrival counters zero when they finish, so the buffer can be reused by the
-    next launch on the same stream without a memset.
+    next launch on the same stream without a memset. A workspace that has to grow is REPLACED, not freed: a CUDA graph
+    captured earlier keeps replaying kernels that carry the old address (the engine keeps several plans, for different batch
+    sizes, on one stream), so the old buffer stays alive for the life of the process. Growing while a stream capture is in
+    progress is refused: the allocation would come out of the graph's private pool.
     """
     s = stream if stream is not None else torch.cuda.current_stream(device)
     key = (torch.device(device).index or 0, int(s.cuda_stream), tag)
     buf = _scratch.get(key)
     if buf is None or buf.numel() < nbytes:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError(f"workspace '{tag}' would have to be (re)allocated during a CUDA graph capture; run the op once "
+                               "eagerly first (the engine's warm-up steps do)")
+        if buf is not None:
+            _retired.append(buf)
         buf = torch.zeros(max(nbytes, 4096), dtype=torch.uint8, device=device)
         _scratch[key] = buf
     return buf

@@ -503,11 +503,13 @@ class MLPTrainEngine:
             cur.wait_event(self._stage_done)     # orders the caller's stream after the staging reads of its tensors
 
     # ------------------------------------------------------------------------------------------ public API
-    def stage(self, x: torch.Tensor, y: torch.Tensor, _paced: bool = True) -> None:
+    def stage(self, x: torch.Tensor, y: torch.Tensor, _paced: bool = True, after: Optional[torch.cuda.Event] = None) -> None:
         """Copy a batch in (H2D from pinned host memory, or straight from a device tensor) and convert it for layer 1
         on the staging stream. Call it for batch i+1 *before* ``step()`` of batch i: the copy and the uint8 -> fp32
         conversion then run concurrently with that step instead of in front of the next one. At most two batches can
-        be staged."""
+        be staged. ``after``: the event that marks ``x`` / ``y`` as produced (a loader's copy-done event); without it the
+        staging stream waits for everything queued on the caller's stream — which, right after a ``step()``, includes that
+        step, and the conversion would then run behind it instead of next to it."""
         if x.shape[0] != self.B:
             raise ValueError(f"engine was built for batches of {self.B} samples (got {x.shape[0]})")
         if len(self._staged) >= 2:
@@ -515,7 +517,10 @@ class MLPTrainEngine:
         slot = self._next_slot
         self._next_slot ^= 1
         st = self.stage_stream
-        st.wait_stream(torch.cuda.current_stream(self.device))     # x / y were produced on the caller's stream
+        if after is not None:
+            st.wait_event(after)
+        else:
+            st.wait_stream(torch.cuda.current_stream(self.device))     # x / y were produced on the caller's stream
         if self._free[slot] is not None:
             st.wait_event(self._free[slot])                          # the step that last read this slot is done
         from_u8 = x.dtype == torch.uint8

@@ -214,7 +214,7 @@ class EngineModel(nn.Module):
         x = _raw_u8(logits.x)
         if logits.training:
             plan.discard_staged()
-            plan.stage(x, y)
+            plan.stage(x, y, after=getattr(logits.x, "_ready", None))
             loss = LazyLoss(self, logits, plan)
             logits._loss = loss
             self._pending = loss

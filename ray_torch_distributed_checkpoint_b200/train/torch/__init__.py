@@ -6,6 +6,7 @@ Mirrors ``ray.train.torch`` as called by the reference: ``get_device()``
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -113,7 +114,7 @@ def _u8_image_source(data_loader):
 
 
 def prepare_data_loader(data_loader, *, add_dist_sampler: bool = True, move_to_device: bool = True,
-                        auto_transfer: bool = True, u8_fast_path: bool = True):
+                        auto_transfer: bool = True, u8_fast_path: bool = True, transfer: Optional[str] = None):
     """Shard a ``DataLoader`` across workers and move its batches to the worker's device (ref:
     ``ray.train.torch.prepare_data_loader`` at ``my_ray_module.py:128-129``).
 
@@ -123,10 +124,13 @@ def prepare_data_loader(data_loader, *, add_dist_sampler: bool = True, move_to_d
     on a side stream, ahead of the consumer.
 
     GPU workers, ``u8_fast_path``: a loader over a uint8 image dataset (FashionMNIST and friends, see
-    ``_u8_image_source``) is replaced by ``data.U8BatchLoader`` — same sampling arithmetic, same batch sizes (tail batch
-    included), but the epoch is gathered in pinned memory by a background thread, pixels and labels cross PCIe as bytes and
-    the batches are ``data.U8Images`` that normalise themselves on the GPU (or are consumed raw by the engine-backed
-    model of :func:`prepare_model`).
+    ``_u8_image_source``) is replaced by ``data.U8BatchLoader`` — same batch sizes (tail batch included), pixels and labels
+    kept as bytes, batches are ``data.U8Images`` that normalise themselves on the GPU (or are consumed raw by the
+    engine-backed model of :func:`prepare_model`). ``transfer`` (default: ``$RTDC_INPUT_TRANSFER`` or ``"auto"``) picks how a
+    shuffled batch reaches the device, see ``data.U8BatchLoader``: ``"resident"`` (dataset uploaded once, exact
+    ``DistributedSampler`` shuffle by a gather kernel; what ``"auto"`` picks when the dataset fits), ``"stream"`` (dataset
+    in pinned host memory, every step's pixels cross PCIe by DMA, two-level block shuffle) or ``"host_gather"`` (exact
+    shuffle gathered by host threads).
     """
     from ...data.loader import DeviceLoader, U8BatchLoader, _claim_timed_loader, shard_data_loader
     import torch.utils.data as tud
@@ -141,7 +145,8 @@ def prepare_data_loader(data_loader, *, add_dist_sampler: bool = True, move_to_d
             shard = add_dist_sampler and world > 1
             return U8BatchLoader(imgs, labels, data_loader.batch_size, device, shuffle=isinstance(data_loader.sampler, tud.RandomSampler),
                                  world=world if shard else 1, rank=rank if shard else 0, drop_last=data_loader.drop_last,
-                                 mean=mean, std=std, wrap=True, timed=timed, lookahead=3)
+                                 mean=mean, std=std, wrap=True, timed=timed, lookahead=3,
+                                 transfer=transfer or os.environ.get("RTDC_INPUT_TRANSFER", "auto"))
     if add_dist_sampler and world > 1:
         data_loader = shard_data_loader(data_loader, world, rank)
     if move_to_device:

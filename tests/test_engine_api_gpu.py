@@ -176,3 +176,38 @@ def test_prepare_data_loader_u8_fast_path_matches_reference_pipeline():
     shuffled = prepare_data_loader(DataLoader(ds, batch_size=250, shuffle=True))
     labels = torch.cat([yb.cpu() for _, yb in shuffled])
     assert sorted(labels.tolist()) == sorted(ds.targets.tolist()) and not torch.equal(labels, ds.targets)
+
+
+def test_loader_transfer_modes_agree_with_their_samplers():
+    from ray_torch_distributed_checkpoint_b200.data import DistributedSampler, FashionMNISTSynthetic, U8BatchLoader
+    ds = FashionMNISTSynthetic(train=False, size=1000)
+    flat = ds.data.reshape(1000, -1)
+    key = lambda rows: {(bytes(r[:16].tolist()), int(r.to(torch.int64).sum())) for r in rows}
+    everything = key(flat)
+    for world in (1, 2):
+        seen = {"resident": set(), "stream": set(), "host_gather": set()}
+        for rank in range(world):
+            want = DistributedSampler(1000, world, rank, shuffle=True, seed=3)
+            want.set_epoch(1)
+            idx = torch.tensor(want.indices())
+            for mode in seen:
+                ld = U8BatchLoader(ds.data, ds.targets, 192, "cuda", shuffle=True, seed=3, world=world, rank=rank, drop_last=False,
+                                   transfer=mode, shuffle_block=64)
+                assert ld.transfer == mode
+                ld.sampler.set_epoch(1)
+                xs, ys = zip(*[(x.cpu(), y.cpu()) for x, y in ld])
+                assert [x.shape[0] for x in xs[:-1]] == [192] * (len(xs) - 1) and len(xs) == len(ld)
+                x, y = torch.cat(xs), torch.cat(ys)
+                if mode != "stream":                                   # exact DistributedSampler order
+                    assert torch.equal(x, flat[idx]) and torch.equal(y, ds.targets[idx])
+                else:                                                  # block shuffle: rows are real rows with their own labels
+                    lut = {k: int(l) for k, l in zip([(bytes(r[:16].tolist()), int(r.to(torch.int64).sum())) for r in flat], ds.targets)}
+                    assert all(lut[(bytes(r[:16].tolist()), int(r.to(torch.int64).sum()))] == int(l) for r, l in zip(x, y))
+                    assert x.shape[0] == len(ld.sampler)
+                seen[mode] |= key(x)
+                ld.close()
+        for mode, got in seen.items():
+            assert got == everything, (mode, world, len(got))          # every sample is visited (padding may repeat a few)
+    # no shuffle: storage order
+    ld = U8BatchLoader(ds.data, ds.targets, 400, "cuda", shuffle=False, drop_last=False, transfer="stream", shuffle_block=128)
+    assert torch.equal(torch.cat([y.cpu() for _, y in ld])[:1000 - 1000 % 128], ds.targets[:1000 - 1000 % 128])

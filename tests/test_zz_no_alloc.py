@@ -39,10 +39,16 @@ def test_colsum_noalloc_matches_colsum_twice_in_a_row():
         x = torch.randn(rows, ld, device="cuda") * (call + 1)
         got = torch.full((cols,), float("nan"), device="cuda")
         ref = torch.full((cols,), float("nan"), device="cuda")
-        before = torch.cuda.memory_allocated()
+        if call == 0:
+            # the first call on a device resolves the built-in scratch's address; make it before measuring free memory
+            assert lib.rtdc_colsum_noalloc(x.data_ptr(), ld, rows, cols, got.data_ptr(), stream) == 0, lib.rtdc_last_error().decode()
+        torch.cuda.synchronize()
+        before, free_before = torch.cuda.memory_allocated(), torch.cuda.mem_get_info()[0]
         rc = lib.rtdc_colsum_noalloc(x.data_ptr(), ld, rows, cols, got.data_ptr(), stream)
         assert rc == 0, lib.rtdc_last_error().decode()
-        assert torch.cuda.memory_allocated() == before          # nothing was taken from torch's allocator either
+        torch.cuda.synchronize()
+        assert torch.cuda.memory_allocated() == before          # nothing was taken from torch's allocator ...
+        assert torch.cuda.mem_get_info()[0] == free_before      # ... and no cudaMalloc happened inside the library either
         need = lib.rtdc_colsum_scratch_bytes(rows, cols)
         scratch = torch.zeros(need, dtype=torch.uint8, device="cuda")
         rc = lib.rtdc_colsum(x.data_ptr(), ld, rows, cols, ref.data_ptr(), scratch.data_ptr(), need, stream)

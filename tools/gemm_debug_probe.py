@@ -1,4 +1,6 @@
 """Component timing of the GEMM kernel with RTDC_GEMM_DEBUG bits (1 no TMA, 2 no MMA, 4 no stores, 8 no split, 16 no fence)."""
+# NOTE: needs a library built with the debug hooks: RTDC_EXTRA_NVCC_FLAGS=-DRTDC_GEMM_DEBUG_HOOKS python -m ray_torch_distributed_checkpoint_b200.ops._build --force
+
 import os, sys
 import torch
 from ray_torch_distributed_checkpoint_b200 import ops

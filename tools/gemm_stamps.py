@@ -1,4 +1,6 @@
 """Per-CTA lifetime of the (persistent) GEMM kernel from its RTDC_GEMM_DEBUG_BUF stamps."""
+# NOTE: needs a library built with the debug hooks: RTDC_EXTRA_NVCC_FLAGS=-DRTDC_GEMM_DEBUG_HOOKS python -m ray_torch_distributed_checkpoint_b200.ops._build --force
+
 import os, sys
 import torch
 from ray_torch_distributed_checkpoint_b200 import ops

@@ -1,4 +1,6 @@
 """Per-CTA timeline of the CTA-pair GEMM kernel from its RTDC_GEMM_DEBUG_BUF stamps ([grid][16] clock64 values)."""
+# NOTE: needs a library built with the debug hooks: RTDC_EXTRA_NVCC_FLAGS=-DRTDC_GEMM_DEBUG_HOOKS python -m ray_torch_distributed_checkpoint_b200.ops._build --force
+
 import os, sys
 import torch
 from ray_torch_distributed_checkpoint_b200 import ops

@@ -1,4 +1,6 @@
 """RTDC_GEMM_DEBUG matrix for the wgrad2 shape (both operands MN-major, split-K) next to the fwd2 shape (K-major)."""
+# NOTE: needs a library built with the debug hooks: RTDC_EXTRA_NVCC_FLAGS=-DRTDC_GEMM_DEBUG_HOOKS python -m ray_torch_distributed_checkpoint_b200.ops._build --force
+
 import os, sys
 import torch
 from ray_torch_distributed_checkpoint_b200 import ops

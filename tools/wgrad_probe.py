@@ -1,4 +1,6 @@
 """wgrad1 / wgrad2 timing (graph replays over rotating operands) for the split-K plan experiments."""
+# NOTE: needs a library built with the debug hooks: RTDC_EXTRA_NVCC_FLAGS=-DRTDC_GEMM_DEBUG_HOOKS python -m ray_torch_distributed_checkpoint_b200.ops._build --force
+
 import os, sys
 import torch
 from ray_torch_distributed_checkpoint_b200 import ops
