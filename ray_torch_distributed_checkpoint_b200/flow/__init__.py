@@ -5,13 +5,14 @@ Covers what the reference's two flows use from Metaflow (``/root/reference/train
 ``Parameter`` (-> CLI flags), ``current`` (incl. ``current.ray_storage_path``, ``current.trigger``,
 ``current.card``), ``Run`` / ``Task`` / ``Flow`` over a local datastore with pickled artifacts, and the
 decorators ``retry``, ``metaflow_ray``, ``kubernetes``, ``pypi``, ``gpu_profile``, ``card``, ``schedule``,
-``trigger_on_finish``. CLI: ``python flow.py run|evaluate [--flag v]``, ``argo-workflows create|trigger``,
+``trigger_on_finish``. CLI: ``python flow.py run|evaluate [--flag v]``, ``argo-workflows create|trigger|serve`` (serve
+honours the ``@schedule`` cron expression on this box),
 ``show``; ``--environment=...`` is accepted and ignored.
 """
 from .core import (FlowSpec, Parameter, Run, Task, Flow, Step, current, step, retry, metaflow_ray, kubernetes, pypi,
-                   gpu_profile, card, schedule, trigger_on_finish, namespace, datastore_root, FlowError)
+                   gpu_profile, card, schedule, trigger_on_finish, namespace, datastore_root, FlowError, CronSchedule)
 from . import cards
 
 __all__ = ["FlowSpec", "Parameter", "Run", "Task", "Flow", "Step", "current", "step", "retry", "metaflow_ray",
            "kubernetes", "pypi", "gpu_profile", "card", "schedule", "trigger_on_finish", "namespace",
-           "datastore_root", "FlowError", "cards"]
+           "datastore_root", "FlowError", "CronSchedule", "cards"]

@@ -594,6 +594,11 @@ class FlowSpec:
         argo_sub = argo.add_subparsers(dest="argo_cmd")
         argo_sub.add_parser("create")
         add_params(argo_sub.add_parser("trigger"))
+        serve = argo_sub.add_parser("serve", help="honour @schedule(cron=...): run the flow at every matching minute")
+        add_params(serve)
+        serve.add_argument("--max-runs", type=int, default=0, help="stop after this many scheduled runs (0: until interrupted)")
+        serve.add_argument("--poll-seconds", type=float, default=1.0)
+        serve.add_argument("--now", default=None, help="pretend the clock starts at this ISO time (tests)")
         sub.add_parser("show")
         args = ap.parse_args(argv)
         if args.datastore:
@@ -607,8 +612,10 @@ class FlowSpec:
             elif args.argo_cmd == "trigger":
                 run_id = self._execute(params)
                 self._fire_downstream(Run(f"{cls.__name__}/{run_id}"))
+            elif args.argo_cmd == "serve":
+                self._serve(params, args.max_runs, args.poll_seconds, args.now)
             else:
-                ap.error("argo-workflows needs 'create' or 'trigger'")
+                ap.error("argo-workflows needs 'create', 'trigger' or 'serve'")
         elif args.cmd == "show":
             print(cls.__name__, "steps:", [k for k, v in vars(cls).items() if getattr(v, "_is_step", False)])
             print("parameters:", {p.name: p.default for p in cls._parameters().values()})
@@ -628,6 +635,31 @@ class FlowSpec:
         sched = rec["decorators"].get("schedule", {}).get("cron")
         trig = rec["decorators"].get("trigger_on_finish", {}).get("flow")
         print(f"[flow] deployed {cls.__name__}" + (f" (cron {sched!r})" if sched else "") + (f" (runs after {trig})" if trig else ""))
+
+    def _serve(self, params: Dict[str, Any], max_runs: int = 0, poll_s: float = 1.0, now: Optional[str] = None):
+        """The scheduler a deployment would get from Argo's CronWorkflow, on this box: at every minute that matches the
+        flow's ``@schedule(cron=...)`` (ref train_flow.py:20, ``*/5 * * * *``) run the flow once, then the flows deployed with
+        ``@trigger_on_finish`` on it. A run that outlasts its slot makes the scheduler skip the slots it overlapped."""
+        import datetime as dt
+        cls = type(self)
+        expr = getattr(cls, "_flow_decos", {}).get("schedule", {}).get("cron")
+        if not expr:
+            raise FlowError(f"{cls.__name__} has no @schedule(cron=...)")
+        cron = CronSchedule(expr)
+        self._deploy()
+        offset = (dt.datetime.fromisoformat(now) - dt.datetime.now()) if now else dt.timedelta(0)
+        runs, last_slot = 0, None
+        print(f"[flow] serving {cls.__name__} on cron {expr!r}; next slot {cron.next_after(dt.datetime.now() + offset):%Y-%m-%d %H:%M}", flush=True)
+        while not max_runs or runs < max_runs:
+            t = (dt.datetime.now() + offset).replace(second=0, microsecond=0)
+            if t != last_slot and cron.matches(t):
+                last_slot = t
+                print(f"[flow] cron slot {t:%Y-%m-%d %H:%M} -> running {cls.__name__}", flush=True)
+                run_id = type(self)(use_cli=False)._execute(dict(params))
+                self._fire_downstream(Run(f"{cls.__name__}/{run_id}"))
+                runs += 1
+                continue
+            time.sleep(poll_s)
 
     @classmethod
     def _fire_downstream(cls, finished: Run):
@@ -651,6 +683,62 @@ class FlowSpec:
             print(f"[flow] {finished.pathspec} finished -> triggering {rec['flow']}", flush=True)
             inst = flow_cls(use_cli=False)
             inst._execute({}, trigger_run=finished)
+
+
+class CronSchedule:
+    """Five-field cron expressions (minute hour day-of-month month day-of-week) with ``*``, lists, ranges and steps —
+    what ``@schedule(cron=...)`` carries (ref train_flow.py:20). Day-of-week 0 and 7 are Sunday; when both day fields are
+    restricted either may match, as in cron."""
+
+    _RANGES = ((0, 59), (0, 23), (1, 31), (1, 12), (0, 7))
+
+    def __init__(self, expr: str):
+        parts = expr.split()
+        if len(parts) != 5:
+            raise ValueError(f"cron expression needs 5 fields (got {expr!r})")
+        self.expr = expr
+        self.fields = [self._parse(p, lo, hi) for p, (lo, hi) in zip(parts, self._RANGES)]
+        self.dom_star, self.dow_star = parts[2] == "*", parts[4] == "*"
+        if 7 in self.fields[4]:
+            self.fields[4].add(0)
+
+    @staticmethod
+    def _parse(field: str, lo: int, hi: int) -> set:
+        out = set()
+        for part in field.split(","):
+            step = 1
+            if "/" in part:
+                part, st = part.split("/", 1)
+                step = int(st)
+            if part in ("*", ""):
+                a, b = lo, hi
+            elif "-" in part:
+                a, b = (int(x) for x in part.split("-", 1))
+            else:
+                a = int(part)
+                b = hi if step > 1 else a
+            if a < lo or b > hi or a > b or step < 1:
+                raise ValueError(f"cron field {field!r} out of range {lo}-{hi}")
+            out.update(range(a, b + 1, step))
+        return out
+
+    def matches(self, t) -> bool:
+        mi, ho, dom, mo, dow = self.fields
+        if t.minute not in mi or t.hour not in ho or t.month not in mo:
+            return False
+        d_ok, w_ok = t.day in dom, (t.isoweekday() % 7) in dow
+        if self.dom_star or self.dow_star:
+            return d_ok and w_ok
+        return d_ok or w_ok
+
+    def next_after(self, t):
+        import datetime as dt
+        t = t.replace(second=0, microsecond=0) + dt.timedelta(minutes=1)
+        for _ in range(366 * 24 * 60):
+            if self.matches(t):
+                return t
+            t += dt.timedelta(minutes=1)
+        raise ValueError(f"cron expression {self.expr!r} never fires")
 
 
 def run_flow(flow_cls, trigger_run: Optional[Run] = None, **params) -> Run:

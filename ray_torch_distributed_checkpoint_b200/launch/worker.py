@@ -29,7 +29,7 @@ def main(payload_path: str) -> int:
     rank = int(os.environ["RANK"])
     world = int(os.environ["WORLD_SIZE"])
     local_rank = int(os.environ.get("LOCAL_RANK", rank))
-    link = SocketLink(payload["socket"], payload["authkey"], rank)
+    link = SocketLink(payload["socket"], payload["authkey"], rank, heartbeat_s=payload.get("heartbeat_s", 0.0))
     try:
         import torch
         import torch.distributed as dist

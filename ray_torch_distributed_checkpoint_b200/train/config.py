@@ -73,12 +73,17 @@ class FailureConfig:
 class RunConfig:
     name: Optional[str] = None
     storage_path: Optional[str] = None
+    storage_filesystem: Optional[Any] = None     # a pyarrow.fs.FileSystem; storage_path is then a path inside it
     checkpoint_config: Optional[CheckpointConfig] = None
     failure_config: Optional[FailureConfig] = None
     verbose: int = 1
     log_to_file: bool = False
     worker_start_timeout_s: float = 300.0   # ref: @metaflow_ray(all_nodes_started_timeout=300), train_flow.py:42
-    worker_report_timeout_s: Optional[float] = None
+    # fit() fails the attempt when no worker message (report, heartbeat) arrives for this long: a rank stuck in host code
+    # would otherwise stall the group forever (device-side waits are bounded separately). Workers send a heartbeat every
+    # worker_heartbeat_s from a background thread, so a long epoch without report() calls does not trip it. None disables.
+    worker_report_timeout_s: Optional[float] = 600.0
+    worker_heartbeat_s: float = 5.0
     callbacks: Optional[list] = None
 
     def __post_init__(self):

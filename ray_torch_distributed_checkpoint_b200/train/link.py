@@ -84,14 +84,31 @@ class DriverServer:
 class SocketLink:
     """Worker end of the channel."""
 
-    def __init__(self, socket_path: str, authkey: bytes, rank: int):
+    def __init__(self, socket_path: str, authkey: bytes, rank: int, heartbeat_s: float = 0.0):
         self.rank = rank
         self.conn = Client(address=socket_path, family="AF_UNIX", authkey=authkey)
-        self.conn.send({"type": "hello", "rank": rank, "pid": os.getpid()})
+        self._send_lock = threading.Lock()       # the heartbeat thread shares the connection's send side
+        self._send({"type": "hello", "rank": rank, "pid": os.getpid()})
         self._ckpt_flags: Dict[int, bool] = {}
+        self._stop = threading.Event()
+        if heartbeat_s and heartbeat_s > 0:
+            threading.Thread(target=self._beat, args=(float(heartbeat_s),), name="rtdc-heartbeat", daemon=True).start()
+
+    def _send(self, msg: dict):
+        with self._send_lock:
+            self.conn.send(msg)
+
+    def _beat(self, period: float):
+        """Tell the driver this process is alive (a host-side hang stops the beats: a thread stuck holding the GIL
+        forever, a dead process; the driver then fails the attempt after RunConfig.worker_report_timeout_s)."""
+        while not self._stop.wait(period):
+            try:
+                self._send({"type": "heartbeat"})
+            except (OSError, EOFError, BrokenPipeError, ValueError):
+                return
 
     def report(self, rank: int, index: int, metrics: Dict[str, Any], checkpoint_path: Optional[str]):
-        self.conn.send({"type": "report", "index": index, "metrics": metrics, "checkpoint_path": checkpoint_path})
+        self._send({"type": "report", "index": index, "metrics": metrics, "checkpoint_path": checkpoint_path})
         while True:
             msg = self.conn.recv()          # blocks: this is the barrier
             if msg["type"] == "ack" and msg["index"] == index:
@@ -104,15 +121,18 @@ class SocketLink:
         return self._ckpt_flags.pop(index, False)
 
     def done(self):
-        self.conn.send({"type": "done"})
+        self._stop.set()
+        self._send({"type": "done"})
 
     def error(self, tb: str):
+        self._stop.set()
         try:
-            self.conn.send({"type": "error", "traceback": tb})
+            self._send({"type": "error", "traceback": tb})
         except (OSError, EOFError, BrokenPipeError):
             pass
 
     def close(self):
+        self._stop.set()
         try:
             self.conn.close()
         except OSError:

@@ -37,17 +37,83 @@ def checkpoint_dir_name(index: int) -> str:
 
 
 class StorageContext:
-    """Resolves where a run lives and moves checkpoint files there."""
+    """Resolves where a run lives and moves checkpoint files there.
 
-    def __init__(self, storage_path: str, experiment_name: Optional[str] = None, trial_name: Optional[str] = None):
+    ``storage_path`` may be a local path / ``file://`` URI (the run directory is built in place), or anything ``pyarrow.fs``
+    can address — an ``s3://`` / ``gs://`` / ``hdfs://`` URI, or any path together with an explicit ``storage_filesystem``
+    (``RunConfig(storage_filesystem=...)``, as in Ray). Remote runs are staged in a local directory that all workers of the
+    node share, and the driver mirrors every completed report (checkpoint directory, result.json, progress.csv) to the remote
+    filesystem and applies retention there too; ``Result.path`` and the ``Checkpoint`` handles then point at the remote copy
+    (ref: ``storage_path=current.ray_storage_path``, a datastore URI, train_flow.py:65 / README.md:13-15)."""
+
+    def __init__(self, storage_path: str, experiment_name: Optional[str] = None, trial_name: Optional[str] = None,
+                 storage_filesystem: Optional[Any] = None):
         local, scheme = _strip_scheme(storage_path)
-        if scheme not in ("local", "file"):
-            raise NotImplementedError(
-                f"storage_path scheme '{scheme}://' is not reachable from this single-node runtime; "
-                "use a local path or file:// URI (a mounted object store works)")
+        self.remote_fs, self.remote_root = None, None
+        if storage_filesystem is not None or scheme not in ("local", "file"):
+            import hashlib
+            import pyarrow.fs as pafs
+            if storage_filesystem is not None:
+                self.remote_fs, self.remote_root = storage_filesystem, str(storage_path).rstrip("/")
+            else:
+                try:
+                    self.remote_fs, self.remote_root = pafs.FileSystem.from_uri(storage_path)
+                except Exception as e:
+                    raise ValueError(f"storage_path {storage_path!r} is neither a local path nor a URI pyarrow.fs can open: {e}") from e
+                self.remote_root = self.remote_root.rstrip("/")
+            tag = hashlib.sha1(f"{type(self.remote_fs).__name__}:{storage_path}".encode()).hexdigest()[:12]
+            local = os.path.join(os.environ.get("RTDC_STAGING_DIR", os.path.expanduser("~/.cache/rtdc_staging")), tag)
+        self.storage_uri = str(storage_path)
         self.storage_path = os.path.abspath(os.path.expanduser(local))
         self.experiment_name = experiment_name or f"TorchTrainer_{_timestamp()}"
         self.trial_name = trial_name or f"TorchTrainer_{uuid.uuid4().hex[:5]}_00000_0_{_timestamp()}"
+
+    # -------------------------------------------------------------- remote mirror (driver side)
+    @property
+    def is_remote(self) -> bool:
+        return self.remote_fs is not None
+
+    @property
+    def remote_trial_path(self) -> Optional[str]:
+        return f"{self.remote_root}/{self.experiment_name}/{self.trial_name}" if self.is_remote else None
+
+    @property
+    def result_path(self) -> str:
+        """What ``Result.path`` reports: the remote trial directory for remote storage, else the local one."""
+        if not self.is_remote:
+            return self.trial_path
+        return self.storage_uri.rstrip("/") + f"/{self.experiment_name}/{self.trial_name}"
+
+    def mirror_checkpoint(self, index: int) -> "Checkpoint":
+        """Upload ``checkpoint_{index}`` of the staging directory; return the handle of the remote copy."""
+        import pyarrow.fs as pafs
+        dst = f"{self.remote_trial_path}/{checkpoint_dir_name(index)}"
+        self.remote_fs.create_dir(dst, recursive=True)
+        pafs.copy_files(self.checkpoint_path(index), dst, source_filesystem=pafs.LocalFileSystem(), destination_filesystem=self.remote_fs)
+        return Checkpoint(dst, filesystem=self.remote_fs)
+
+    def mirror_logs(self):
+        import pyarrow.fs as pafs
+        self.remote_fs.create_dir(self.remote_trial_path, recursive=True)
+        for name in ("result.json", "progress.csv", "params.json"):
+            src = os.path.join(self.trial_path, name)
+            if os.path.exists(src):
+                pafs.copy_files(src, f"{self.remote_trial_path}/{name}", source_filesystem=pafs.LocalFileSystem(),
+                                destination_filesystem=self.remote_fs)
+
+    def delete_checkpoint(self, checkpoint: "Checkpoint"):
+        """Retention: remove a checkpoint directory (and, for remote storage, its staged local twin)."""
+        local = checkpoint._local_path()
+        if local and os.path.isdir(local):
+            shutil.rmtree(local, ignore_errors=True)
+            return
+        if self.is_remote:
+            try:
+                self.remote_fs.delete_dir(checkpoint.path)
+            except Exception:
+                pass
+            twin = os.path.join(self.trial_path, os.path.basename(checkpoint.path.rstrip("/")))
+            shutil.rmtree(twin, ignore_errors=True)
 
     @property
     def experiment_path(self) -> str:
@@ -102,8 +168,9 @@ class StorageContext:
 class CheckpointManager:
     """Driver-side registry of persisted checkpoints + retention (``num_to_keep``)."""
 
-    def __init__(self, config: CheckpointConfig):
+    def __init__(self, config: CheckpointConfig, delete=None):
         self.config = config
+        self._delete = delete            # how to remove a checkpoint that fell out of retention (StorageContext.delete_checkpoint)
         self._entries: List[Tuple[Checkpoint, Dict[str, Any], int]] = []   # (checkpoint, metrics, index)
         self._lock = threading.Lock()
 
@@ -143,9 +210,12 @@ class CheckpointManager:
                 doomed.append(e)
             for e in doomed:
                 self._entries.remove(e)
-                local = e[0]._local_path()
-                if local and os.path.isdir(local):
-                    shutil.rmtree(local, ignore_errors=True)
+                if self._delete is not None:
+                    self._delete(e[0])
+                else:
+                    local = e[0]._local_path()
+                    if local and os.path.isdir(local):
+                        shutil.rmtree(local, ignore_errors=True)
             return [e[0] for e in doomed]
 
 

@@ -59,7 +59,7 @@ class _Bookkeeper:
 
     def __init__(self, storage: StorageContext, run_config: RunConfig, params: Dict[str, Any]):
         self.storage = storage
-        self.manager = CheckpointManager(run_config.checkpoint_config)
+        self.manager = CheckpointManager(run_config.checkpoint_config, delete=storage.delete_checkpoint)
         self.logger = ResultLogger(storage.trial_path, params)
         self.history: List[Dict[str, Any]] = []
         self.start_time = time.time()
@@ -78,19 +78,24 @@ class _Bookkeeper:
         self.history.append(row)
         self.logger.log(row)
         if has_ckpt:
-            ckpt = Checkpoint.from_directory(self.storage.checkpoint_path(index))
+            if self.storage.is_remote:
+                ckpt = self.storage.mirror_checkpoint(index)
+            else:
+                ckpt = Checkpoint.from_directory(self.storage.checkpoint_path(index))
             removed = self.manager.register(ckpt, row, index)
             for c in removed:
                 _log(self.verbose > 1, f"retention: removed {c.path}")
         shown = {k: v for k, v in metrics.items() if not k.startswith("_")}
         _log(self.verbose, f"report {index + 1}: {shown}" + (f"  checkpoint -> {checkpoint_dir_name(index)}" if has_ckpt else ""))
+        if self.storage.is_remote:
+            self.storage.mirror_logs()
         for cb in self.callbacks:
             cb(index, row)
         return has_ckpt
 
     def result(self, error: Optional[Exception] = None) -> Result:
         return Result(metrics=self.history[-1] if self.history else None, checkpoint=self.manager.latest,
-                      error=error, path=self.storage.trial_path, metrics_history=list(self.history),
+                      error=error, path=self.storage.result_path, metrics_history=list(self.history),
                       best_checkpoints=self.manager.best_checkpoints)
 
 
@@ -127,7 +132,7 @@ class TorchTrainer:
         from ..launch.group import WorkerGroup, worker_argv
 
         rc, sc = self.run_config, self.scaling_config
-        storage = StorageContext(rc.storage_path, rc.name)
+        storage = StorageContext(rc.storage_path, rc.name, storage_filesystem=rc.storage_filesystem)
         storage.make_dirs()
         book = _Bookkeeper(storage, rc, self._params())
         if sc.use_gpu:
@@ -172,6 +177,7 @@ class TorchTrainer:
                 "storage": storage, "use_gpu": sc.use_gpu, "backend": sc.backend, "start_checkpoint": start_ckpt,
                 "start_index": next_index, "socket": sock, "authkey": authkey, "sys_path": list(sys.path),
                 "experiment_name": storage.experiment_name, "trial_name": storage.trial_name,
+                "heartbeat_s": rc.worker_heartbeat_s if rc.worker_report_timeout_s else 0.0,
             }, f)
         server = DriverServer(sock, sc.num_workers, authkey)
         # workers must be able to import whatever module the training function lives in
@@ -194,6 +200,8 @@ class TorchTrainer:
                     kind = ev["type"]
                     if kind == "hello":
                         hello_ranks.add(ev["rank"])
+                    elif kind == "heartbeat":
+                        pass                                   # liveness only: last_progress was refreshed above
                     elif kind == "report":
                         idx = ev["index"]
                         pending.setdefault(idx, []).append(ev)
@@ -260,11 +268,11 @@ class TorchTrainer:
             torch.cuda.set_device(local_rank)
         names = [rc.name, None]
         if rank == 0:
-            s0 = StorageContext(rc.storage_path, rc.name)
+            s0 = StorageContext(rc.storage_path, rc.name, storage_filesystem=rc.storage_filesystem)
             names = [s0.experiment_name, s0.trial_name]
         if world > 1:
             dist.broadcast_object_list(names, src=0)
-        storage = StorageContext(rc.storage_path, names[0], names[1])
+        storage = StorageContext(rc.storage_path, names[0], names[1], storage_filesystem=rc.storage_filesystem)
         book = None
         if rank == 0:
             storage.make_dirs()

@@ -125,3 +125,23 @@ def test_trigger_on_finish_chain(datastore):
     assert "triggering RayTorchEval" in out
     ev = flow.Flow("RayTorchEval").latest_successful_run
     assert ev is not None and ev._meta()["triggered_by"].startswith("RayTorchTrain/")
+
+
+def test_cron_schedule_and_serve_loop(datastore):
+    import datetime as dt
+    from ray_torch_distributed_checkpoint_b200.flow import CronSchedule
+    every5 = CronSchedule("*/5 * * * *")                             # the reference's schedule (train_flow.py:20)
+    assert every5.matches(dt.datetime(2026, 1, 1, 10, 35)) and not every5.matches(dt.datetime(2026, 1, 1, 10, 36))
+    assert every5.next_after(dt.datetime(2026, 1, 1, 10, 36, 12)) == dt.datetime(2026, 1, 1, 10, 40)
+    wk = CronSchedule("30 2 * * 1-5")
+    assert wk.matches(dt.datetime(2026, 11, 6, 2, 30)) and not wk.matches(dt.datetime(2026, 11, 7, 2, 30))    # Fri yes, Sat no
+    assert CronSchedule("0 0 1,15 * 0").matches(dt.datetime(2026, 11, 8, 0, 0))                                   # Sunday OR day-of-month
+    with pytest.raises(ValueError):
+        CronSchedule("61 * * * *")
+    # the serve loop fires the scheduled flow at a matching minute and chains the deployed eval flow after it
+    env = dict(os.environ, RTDC_FLOW_DATASTORE=datastore, RTDC_TRAIN_SIZE="256", RTDC_TEST_SIZE="64", RTDC_FLOW_GPU="0")
+    _run([os.path.join(EX, "eval_flow.py"), "argo-workflows", "create"], env)
+    out = _run([os.path.join(EX, "train_flow.py"), "argo-workflows", "serve", "--max-runs", "1", "--poll-seconds", "0.05",
+                "--now", "2026-01-01T10:35:00", "--epochs", "1", "--batch_size", "64"], env)
+    assert "cron slot 2026-01-01 10:35 -> running RayTorchTrain" in out and "triggering RayTorchEval" in out
+    assert flow.Flow("RayTorchTrain").latest_successful_run is not None

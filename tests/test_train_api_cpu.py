@@ -87,8 +87,8 @@ def test_persist_rank0_wins(tmp_path):
     assert open(os.path.join(dst, "latest_model.pt")).read() == "rank0"
     assert os.path.exists(os.path.join(dst, "only_rank1.bin"))
     assert not [f for f in os.listdir(dst) if f.endswith(".tmp")]
-    with pytest.raises(NotImplementedError):
-        StorageContext("s3://bucket/x")
+    with pytest.raises(ValueError):
+        StorageContext("nosuchscheme://bucket/x")            # remote URIs go through pyarrow.fs; unknown schemes are refused
 
 
 def _loop(config):
@@ -166,3 +166,48 @@ def test_session_functions_outside_fit():
         train.report({"a": 1})
     from ray_torch_distributed_checkpoint_b200.train.torch import get_device
     assert get_device().type == "cpu"
+
+
+def _remote_loop(config):
+    import tempfile
+    for i in range(3):
+        d = tempfile.mkdtemp()
+        torch.save({"i": i}, os.path.join(d, "latest_model.pt"))
+        train.report({"i": i}, checkpoint=Checkpoint.from_directory(d))
+
+
+def test_remote_storage_through_pyarrow_filesystem(tmp_path, monkeypatch):
+    """A storage_path that is not a local directory (ref: a datastore URI, train_flow.py:65): staged locally, mirrored through
+    pyarrow.fs after every report, retention applied on the remote side, Result / Checkpoint handles point at the remote copy."""
+    import pyarrow.fs as pafs
+    bucket = tmp_path / "bucket"
+    bucket.mkdir()
+    monkeypatch.setenv("RTDC_STAGING_DIR", str(tmp_path / "staging"))
+    fs = pafs.SubTreeFileSystem(str(bucket), pafs.LocalFileSystem())
+    trainer = TorchTrainer(_remote_loop, scaling_config=ScalingConfig(num_workers=1, use_gpu=False),
+                           run_config=RunConfig(storage_path="runs/exp", storage_filesystem=fs, name="remote",
+                                                checkpoint_config=CheckpointConfig(num_to_keep=2), verbose=0))
+    result = trainer.fit()
+    assert result.path.startswith("runs/exp/remote/") and result.checkpoint.filesystem is not None
+    trial = bucket / result.path
+    assert sorted(p.name for p in trial.iterdir() if p.name.startswith("checkpoint_")) == ["checkpoint_000001", "checkpoint_000002"]
+    assert (trial / "result.json").exists() and (trial / "progress.csv").exists()
+    with result.checkpoint.as_directory() as d:                      # downloaded to a temp dir, removed afterwards
+        assert not d.startswith(str(bucket)) and torch.load(os.path.join(d, "latest_model.pt"))["i"] == 2
+    assert pickle.loads(pickle.dumps(result)).checkpoint.path == result.checkpoint.path
+    with pytest.raises(ValueError):
+        StorageContext("nosuchscheme://bucket/x")
+
+
+def test_heartbeat_timeout_fails_a_silent_worker(tmp_path):
+    def stuck(config):
+        import time
+        from ray_torch_distributed_checkpoint_b200.train import session
+        session._get_session("x").link._stop.set()                   # a worker whose host side went silent
+        time.sleep(30)
+
+    trainer = TorchTrainer(stuck, scaling_config=ScalingConfig(num_workers=1, use_gpu=False),
+                           run_config=RunConfig(storage_path=str(tmp_path), verbose=0, worker_report_timeout_s=2.0, worker_heartbeat_s=0.2))
+    with pytest.raises(TrainingFailedError, match="no worker activity"):
+        trainer.fit()
+    assert RunConfig().worker_report_timeout_s == 600.0               # finite by default
