@@ -200,6 +200,12 @@ def run_ours(args):
             e2e_blocks.append(max(t["end_ms_since_first_begin"][hi - 1] - t["end_ms_since_first_begin"][lo - 1] for t in per_rank))
         ms, ms_min, ms_max = _median_block(dev_blocks)
         e2e_ms, e2e_min, e2e_max = _median_block(e2e_blocks)
+        # host side: time between consecutive batches being handed to the loop (within an epoch), worst rank's median
+        host_gaps = []
+        for t in per_rank:
+            hb = t["host_begin_s"]
+            gaps = sorted(hb[i + 1] - hb[i] for i in range(warm_epochs * S, n - 1) if (i + 1) % S)
+            host_gaps.append(gaps[len(gaps) // 2] * 1e3 if gaps else 0.0)
         extra = per_rank[0].get("extra", {})
         lps = int(extra.get("launches_per_train_step", 0))
         gb = B * world
@@ -229,6 +235,7 @@ def run_ours(args):
             "gpu_launches": lps * K,
             "gpu_launches_per_step": lps,
             "tflops_fp32_equiv": round(flops / (ms / 1e3) / 1e12, 2),
+            "host_ms_per_step": round(max(host_gaps), 4),
             "fit_wall_s": round(wall, 2),
             "final_metrics": {k: v for k, v in (getattr(result, "metrics", None) or {}).items() if not str(k).startswith("_")},
         }

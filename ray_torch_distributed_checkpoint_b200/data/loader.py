@@ -53,6 +53,22 @@ class DistributedSampler(Sampler):
             idx = idx[:self.total_size]
         return idx[self.rank:self.total_size:self.num_replicas]
 
+    def indices_tensor(self, dtype=torch.int64) -> torch.Tensor:
+        """:meth:`indices` without Python lists (same values): what a loader over hundreds of thousands of rows wants."""
+        if self.shuffle:
+            g = torch.Generator()
+            g.manual_seed(self.seed + self.epoch)
+            idx = torch.randperm(self.n, generator=g)
+        else:
+            idx = torch.arange(self.n)
+        if not self.drop_last:
+            pad = self.total_size - self.n
+            if pad > 0:
+                idx = torch.cat([idx] + [idx] * (pad // max(1, self.n)) + [idx[:pad % max(1, self.n)]])
+        else:
+            idx = idx[:self.total_size]
+        return idx[self.rank:self.total_size:self.num_replicas].to(dtype).contiguous()
+
     def __iter__(self) -> Iterator[int]:
         return iter(self.indices())
 
@@ -423,8 +439,9 @@ class U8BatchLoader:
         self.normalize, self.mean, self.std = normalize, mean, std
         self.wrap, self.timed = wrap, timed
         self.lookahead = max(1, int(lookahead))
-        self._prepared = {}          # host_gather: epoch -> (slot, thread)
+        self._prepared = {}          # epoch -> (slot, thread, result box) of the background plan
         self._closed = False
+        self._iterated_epoch = None
 
         if transfer == "stream":
             self.sampler = BlockSampler(n_rows, shuffle_block, world, rank, shuffle=shuffle, seed=seed)
@@ -468,9 +485,8 @@ class U8BatchLoader:
         if timed:
             TIMING["extra"]["h2d_bytes_per_step"] = self.h2d_bytes_per_batch
             TIMING["extra"]["input_transfer"] = transfer
-        if transfer == "host_gather":
-            _register_for_exit(self)
-            self._prepare(self.sampler.epoch)
+        _register_for_exit(self)
+        self._prepare(self.sampler.epoch)
 
     @property
     def dataset(self):
@@ -481,28 +497,63 @@ class U8BatchLoader:
         return n // self.batch_size if self.drop_last else math.ceil(n / self.batch_size)
 
     def close(self):
-        """Join the background shuffle threads (host_gather)."""
+        """Join the background epoch-plan threads."""
         self._closed = True
         for e in list(self._prepared):
             self._prepared.pop(e)[1].join()
 
-    # ---------------------------------------------------------------- host_gather: epoch permutation (background)
+    # ---------------------------------------------------------------- per-epoch host-side plan (background thread)
+    def _plan(self, epoch: int, slot: int):
+        """Everything the host has to compute for an epoch, done off the training thread while the previous epoch runs:
+        the permutation (resident: int32 indices into a pinned buffer; stream: block order + the shard's labels;
+        host_gather: the gathered pixel / label shard)."""
+        old_epoch = self.sampler.epoch
+        self.sampler.set_epoch(epoch)
+        try:
+            if self.transfer == "stream":
+                starts = torch.as_tensor(self.sampler.block_starts(), dtype=torch.int64)
+                G = self.sampler.block
+                torch.index_select(self.labels.view(-1), 0, (starts[:, None] + torch.arange(G)[None, :]).reshape(-1), out=self._host_y[slot])
+                return starts
+            idx = self.sampler.indices_tensor()
+        finally:
+            self.sampler.set_epoch(old_epoch)
+        if self.transfer == "resident":
+            self._host_idx[slot].copy_(idx)
+            return None
+        torch.index_select(self.images, 0, idx, out=self._host_x[slot])
+        torch.index_select(self.labels, 0, idx, out=self._host_y[slot])
+        return None
+
     def _prepare(self, epoch: int):
         if epoch in self._prepared or self._closed:
             return
         slot = epoch % 2
-        old_epoch = self.sampler.epoch
-        self.sampler.set_epoch(epoch)
-        idx = torch.as_tensor(self.sampler.indices(), dtype=torch.int64)
-        self.sampler.set_epoch(old_epoch)
+        box = {}
 
         def work():
-            torch.index_select(self.images, 0, idx, out=self._host_x[slot])
-            torch.index_select(self.labels, 0, idx, out=self._host_y[slot])
+            try:
+                box["plan"] = self._plan(epoch, slot)
+            except BaseException as e:          # surfaced when the epoch is iterated
+                box["error"] = e
 
-        th = threading.Thread(target=work, name="rtdc-epoch-permute", daemon=True)
+        th = threading.Thread(target=work, name="rtdc-epoch-plan", daemon=True)
         th.start()
-        self._prepared[epoch] = (slot, th)
+        self._prepared[epoch] = (slot, th, box)
+
+    def _take_plan(self, epoch: int):
+        """Join (or compute) the plan of ``epoch``; start the next epoch's."""
+        self._prepare(epoch)
+        slot, th, box = self._prepared.pop(epoch)
+        th.join()
+        for e in list(self._prepared):          # stale preparations (epoch set backwards)
+            if e != epoch + 1:
+                self._prepared.pop(e)[1].join()
+        if "error" in box:
+            raise box["error"]
+        if len(self) > 1 and self.prefetch_next_epoch and self.sampler.shuffle:
+            self._prepare(epoch + 1)            # next epoch's shuffle overlaps this epoch's training
+        return slot, box.get("plan")
 
     def _emit(self, xb: torch.Tensor, yb: torch.Tensor, ready=None):
         if self.normalize or not self.wrap:
@@ -513,15 +564,8 @@ class U8BatchLoader:
 
     # ---------------------------------------------------------------- per-epoch set-up of each transfer
     def _epoch_host_gather(self, epoch: int):
-        self._prepare(epoch)
-        slot, th = self._prepared.pop(epoch)
-        th.join()
-        for e in list(self._prepared):          # stale preparations (epoch set backwards)
-            if e != epoch + 1:
-                self._prepared.pop(e)[1].join()
+        slot, _ = self._take_plan(epoch)
         hx, hy = self._host_x[slot], self._host_y[slot]
-        if len(self) > 1 and self.prefetch_next_epoch:
-            self._prepare(epoch + 1)            # next epoch's shuffle overlaps this epoch's training
 
         def fill(bi, lo, hi):
             self._dev_x[bi][:hi - lo].copy_(hx[lo:hi], non_blocking=True)
@@ -537,8 +581,7 @@ class U8BatchLoader:
 
     def _epoch_resident(self, epoch: int):
         from ..ops import u8_gather_rows
-        slot = epoch % 2
-        self._host_idx[slot].copy_(torch.as_tensor(self.sampler.indices(), dtype=torch.int32))
+        slot, _ = self._take_plan(epoch)
         with torch.cuda.stream(self.copy_stream):
             self._dev_idx[slot].copy_(self._host_idx[slot], non_blocking=True)
         idx = self._dev_idx[slot]
@@ -549,28 +592,33 @@ class U8BatchLoader:
 
     def _epoch_stream(self, epoch: int):
         from ..ops import h2d_pieces
-        slot = epoch % 2
-        starts = torch.as_tensor(self.sampler.block_starts(), dtype=torch.int64)
+        slot, starts = self._take_plan(epoch)
         G = self.sampler.block
         hy = self._host_y[slot]
-        # this epoch's labels in shard order: a few hundred KB, gathered here once; the pixels are never gathered on the host
-        torch.index_select(self.labels.view(-1), 0, (starts[:, None] + torch.arange(G)[None, :]).reshape(-1), out=hy)
         row = self.row
+        starts_l = starts.tolist()
 
         def fill(bi, lo, hi):
             b0, b1 = lo // G, (hi - 1) // G
-            offs = starts[b0:b1 + 1] * row
-            sizes = torch.full((b1 - b0 + 1,), G * row, dtype=torch.int64)
+            offs = [s_ * row for s_ in starts_l[b0:b1 + 1]]
+            sizes = [G * row] * (b1 - b0 + 1)
             head = lo - b0 * G                                   # the window may start / end inside a block
             offs[0] += head * row
             sizes[0] -= head * row
             sizes[-1] -= ((b1 + 1) * G - hi) * row
-            h2d_pieces(self._dev_x[bi], self.images, offs, sizes, stream=self.copy_stream)
+            h2d_pieces(self._dev_x[bi], self.images, torch.tensor(offs, dtype=torch.int64), torch.tensor(sizes, dtype=torch.int64),
+                       stream=self.copy_stream)
             self._copy_labels(bi, hy, lo, hi)
         return fill, None
 
     def __iter__(self):
         epoch = self.sampler.epoch
+        if self.sampler.shuffle and self._iterated_epoch == epoch:
+            # nobody called sampler.set_epoch since the last pass (single-worker loops do not, my_ray_module.py:149-151):
+            # reshuffle anyway, like the RandomSampler of the DataLoader this loader stands in for
+            epoch += 1
+            self.sampler.set_epoch(epoch)
+        self._iterated_epoch = epoch
         nb, bs = len(self), self.batch_size
         total = len(self.sampler)
         if not self.cuda:
