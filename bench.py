@@ -300,6 +300,21 @@ def run_ours_engine(args):
             barrier()
             blocks.append(_max_over_ranks(e0.elapsed_time(e1), dev))
     ms, ms_min, ms_max = _median_block(blocks)
+    if args.kernel_trace and rank == 0:
+        # which kernels run inside a step on this rank (CUPTI through torch.profiler; not part of any timed region)
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for i in range(3):
+                eng.step(dev_x[i % rot], dev_y[i % rot])
+            torch.cuda.synchronize(dev)
+        rows = sorted(((e.key, e.count, e.device_time_total) for e in prof.key_averages() if e.device_time_total > 0), key=lambda r: -r[2])
+        with open(args.kernel_trace, "w") as f:
+            f.write(f"# kernels of 3 training steps on rank 0 of {world} GPU(s), ar_mode={eng.ar_mode}, algo={args.algo} (torch.profiler / CUPTI)\n")
+            f.write("# name | launches | total device us\n")
+            for name, cnt, us in rows:
+                f.write(f"{name} | {cnt} | {us:.1f}\n")
+    if world > 1:
+        dist.barrier()
     launches_per_step = eng.kernel_launches_per_step.get("train_u8", 0)
     final_loss = float(eng.loss.item())
 
@@ -476,6 +491,7 @@ def main():
     ap.add_argument("--lookahead", type=int, default=3, help="H2D batches in flight ahead of the consumer (ours-engine e2e loop)")
     ap.add_argument("--algo", default="auto", choices=["auto", "two_shot", "nvls"])
     ap.add_argument("--ar-mode", default=None, choices=["fused", "merged", "bucketed"])
+    ap.add_argument("--kernel-trace", default=None, help="ours-engine: write the kernel names of 3 steps on rank 0 to this file")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

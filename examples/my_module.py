@@ -131,6 +131,7 @@ def train_func_per_worker(config: Dict):
     checkpointer = ckpt.AsyncCheckpointer(device) if rank == 0 else None
 
     t0_full = time.time()
+    phases = {"train": 0.0, "validate": 0.0, "checkpoint": 0.0, "report": 0.0}     # host seconds per phase (RTDC_PROFILE_EPOCHS)
     for epoch in range(start_epoch, epochs):
         t0 = time.time()
         if world > 1:
@@ -143,6 +144,7 @@ def train_func_per_worker(config: Dict):
             loss.backward()
             optimizer.step()
 
+        t1 = time.time()
         model.eval()
         metrics = EvalAccumulator(model)                      # loss sum and correct count stay on the device
         with torch.no_grad():
@@ -153,6 +155,7 @@ def train_func_per_worker(config: Dict):
         val_loss, accuracy = metrics.compute()                # the epoch's only device->host sync
         val_losses.append(val_loss)
         val_acc.append(accuracy)
+        t2 = time.time()
 
         pending = None
         if rank == 0:
@@ -162,12 +165,19 @@ def train_func_per_worker(config: Dict):
             pending = checkpointer.save(_checkpoint_state(epoch, model, optimizer, val_losses, val_acc),
                                         tempfile.mkdtemp(prefix="rtdc_ckpt_"), names)
         best_val_loss = min(best_val_loss, val_loss)
+        t3 = time.time()
         # every rank reports; the checkpoint write, its persistence and the cross-worker barrier finish in
         # the background while the next epoch trains
         train.report({"val_loss": val_loss, "accuracy": accuracy, "epoch": epoch}, checkpoint=pending,
                      checkpoint_upload_mode="async")
+        t4 = time.time()
+        for k, dt in zip(phases, (t1 - t0, t2 - t1, t3 - t2, t4 - t3)):
+            phases[k] += dt
         print(f"[my_module] Model on-device. Last epoch took {round((time.time() - t0) / 60, 3)} minutes. Training model...")
     print(f"[my_module] Training completed in {round((time.time() - t0_full) / 60, 3)} minutes!")
+    if os.environ.get("RTDC_PROFILE_EPOCHS") and epochs > start_epoch:
+        n = epochs - start_epoch
+        print(f"[my_module] rank {rank} host ms per epoch: " + ", ".join(f"{k} {v / n * 1e3:.2f}" for k, v in phases.items()))
 
 
 def train_fashion_mnist(num_workers=1, use_gpu=False, global_batch_size=32, learning_rate=1e-3, epochs=10,

@@ -498,8 +498,10 @@ RTDC_API int rtdc_symm_sgd_step(void* handle, size_t g_offset, size_t p_offset, 
   if (algo != 2 && algo != 3) return fail(RTDC_ERR_ARG, "symm_sgd_step: algo must be 0 (auto), 2 (P2P) or 3 (NVLS)");
   const size_t nvec = count / 4;
   const size_t work = (nvec + info.world - 1) / info.world;
-  int blocks = static_cast<int>((work + AR_THREADS - 1) / AR_THREADS);   // one vector per thread when the pad rows allow it
-  int cap = max_blocks > 0 ? max_blocks : RTDC_SYMM_MAX_BLOCKS;
+  // Latency-bound at the MLP's size: every block is one more participant in both cross-GPU barriers. Measured at 2 GPUs on
+  // the 2.68 MB arena (tools/bench_allreduce.py): 160 blocks 29.7 us, 64 blocks 19.7 us, 32 blocks 21.4 us, 16 blocks 25.6 us.
+  int blocks = static_cast<int>((work + AR_THREADS * 2 - 1) / (AR_THREADS * 2));
+  int cap = max_blocks > 0 ? max_blocks : 64;
   if (cap > RTDC_SYMM_MAX_BLOCKS) cap = RTDC_SYMM_MAX_BLOCKS;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;

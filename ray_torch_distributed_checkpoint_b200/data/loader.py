@@ -454,6 +454,7 @@ class U8BatchLoader:
         self._prepared = {}          # epoch -> (slot, thread, result box) of the background plan
         self._closed = False
         self._iterated_epoch = None
+        self._epoch_copies_done = [None, None]
 
         if transfer == "stream":
             self.sampler = BlockSampler(n_rows, shuffle_block, world, rank, shuffle=shuffle, seed=seed)
@@ -543,8 +544,12 @@ class U8BatchLoader:
         slot = epoch % 2
         box = {}
 
+        done = self._epoch_copies_done[slot] if self.cuda else None
+
         def work():
             try:
+                if done is not None:
+                    done.synchronize()          # the H2D copies of epoch - 2 out of this slot's pinned buffers
                 box["plan"] = self._plan(epoch, slot)
             except BaseException as e:          # surfaced when the epoch is iterated
                 box["error"] = e
@@ -689,5 +694,8 @@ class U8BatchLoader:
             done = torch.cuda.Event()
             done.record(torch.cuda.current_stream(self.device))
             self._free_ev[bi] = done
-        # pinned per-epoch buffers may be rewritten (epoch + 2) only after their last H2D has finished
-        self.copy_stream.synchronize()
+        # pinned per-epoch buffers may be rewritten (by the plan of epoch + 2) only after their last H2D has finished: that plan
+        # thread waits for this event, the training thread does not (it goes on to validation while the GPU drains the epoch)
+        ev = torch.cuda.Event()
+        ev.record(self.copy_stream)
+        self._epoch_copies_done[epoch % 2] = ev
