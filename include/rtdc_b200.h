@@ -78,6 +78,24 @@ typedef struct rtdc_gemm_desc {
   const uint32_t* mask_bits_in; int ld_mask_in;
 } rtdc_gemm_desc;
 
+/* bf16 GEMM (tcgen05.mma kind::f16, fp32 accumulation in TMEM, TMA-fed, persistent): D[M,N] = act(alpha * sum_k A(m,k) B(n,k) + bias[n]).
+ * a_mn / b_mn as in rtdc_gemm_desc (0: [rows, K] row-major; 1: [K, rows] row-major), so forward (x W^T), dgrad (dy W) and wgrad
+ * (dy^T x) of a Linear layer need no transposed copies. Pointers 16-byte aligned, leading dimensions multiples of 8 elements.
+ * out is bf16 (out_fp32 = 0) or fp32 [M, ldo]. splits > 1 (0 = choose; only for fp32 output without bias / activation) splits K over
+ * CTAs that add into the zeroed output with fp32 atomics (wgrad: K = the batch's tokens). act: 0 none, 1 relu, 2 gelu(tanh), 3 gelu(erf).
+ * The reference has no bf16 path (it trains its MLP in fp32, no autocast); this serves the bf16 GPT-2 / ResNet-50 configurations. */
+typedef struct rtdc_gemm_bf16_desc {
+  const void* a; int lda; int a_mn;
+  const void* b; int ldb; int b_mn;
+  int M, N, K;
+  void* out; int ldo; int out_fp32;
+  const void* bias; int bias_fp32;   /* [N] bf16 (or fp32), or NULL */
+  int act;
+  float alpha;                       /* 0 means 1 */
+  int splits;
+} rtdc_gemm_bf16_desc;
+int rtdc_gemm_bf16(const rtdc_gemm_bf16_desc* d, void* stream);
+
 /* out[n] = bias[n] (0 when NULL) + t * sum_k w[n*ldw + k], n < rows: the effective bias of a Linear layer whose input
  * normalisation x = s*raw + t has been folded into the GEMM (see rtdc_gemm_desc.alpha). One warp per row. */
 int rtdc_fold_input_bias(const float* w, int ldw, int rows, int cols, const float* bias, float t, float* out, void* stream);
@@ -201,6 +219,10 @@ int rtdc_sgd_step_advance_log(float* p, const float* g, float* m, size_t n, rtdc
 /* Adam / AdamW (decoupled != 0): step counter lives in hyper_dev->step and is advanced by rtdc_adam_advance. */
 typedef struct rtdc_adam_hyper { float lr, beta1, beta2, eps, weight_decay, grad_scale; int decoupled; int step; } rtdc_adam_hyper;
 int rtdc_adam_step(float* p, const float* g, float* m, float* v, size_t n, const rtdc_adam_hyper* hyper_dev, void* stream);
+/* bf16 parameters: the update runs on the fp32 `master` copy (and fp32 m, v); p_bf16 is rewritten from the master every step,
+ * g_bf16 is the bf16 gradient arena. Same hyper-parameters and step counter. */
+int rtdc_adam_step_bf16(void* p_bf16, const void* g_bf16, float* master, float* m, float* v, size_t n,
+                        const rtdc_adam_hyper* hyper_dev, void* stream);
 int rtdc_adam_advance(rtdc_adam_hyper* hyper_dev, void* stream);
 /* step_counter[0] += 1 on the stream (dropout step counter, first_step flag clearing). */
 int rtdc_counter_advance(uint32_t* counter_dev, rtdc_sgd_hyper* sgd_hyper_or_null, void* stream);

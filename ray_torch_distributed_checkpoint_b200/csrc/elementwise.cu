@@ -2,6 +2,8 @@
 // (K4/K5), deterministic column sums for bias gradients (K6), uint8->fp32 input normalisation
 // (K9 fused with the reference's ToTensor+Normalize), fused multi-tensor SGD / Adam over a flat
 // arena (K7). All are 128-bit vectorised grid-stride kernels sized to 148 SMs x resident CTAs.
+#include <cuda_bf16.h>
+
 #include "common.h"
 #include "ptx.cuh"
 #include "../../include/rtdc_b200.h"
@@ -435,6 +437,57 @@ u8_gather_rows_kernel(const uint8_t* __restrict__ src, const int32_t* __restrict
   }
 }
 
+// Adam / AdamW for bf16 parameters: the update runs on an fp32 master copy (and fp32 moments); the bf16 parameter the model
+// computes with is re-derived from the master every step, the bf16 gradient comes straight from the (all-reduced) gradient arena.
+// One pass over 2 + 2 + 3 x 4 bytes per element, eight elements (one 16-byte bf16 vector) per thread.
+__global__ void __launch_bounds__(256)
+adam_bf16_kernel(__nv_bfloat16* __restrict__ p16, const __nv_bfloat16* __restrict__ g16, float* __restrict__ master, float* __restrict__ m,
+                 float* __restrict__ v, size_t n, const rtdc_adam_hyper* __restrict__ hp) {
+  const rtdc_adam_hyper h = *hp;
+  const float t = static_cast<float>(h.step);
+  const float bc1 = 1.f - powf(h.beta1, t);
+  const float bc2_sqrt = sqrtf(1.f - powf(h.beta2, t));
+  const size_t nvec = n / 8;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    const uint4 graw = __ldg(reinterpret_cast<const uint4*>(g16) + i);
+    const uint32_t gw[4] = {graw.x, graw.y, graw.z, graw.w};
+    float pv[8], mv[8], vv[8];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const float4 a = reinterpret_cast<const float4*>(master)[2 * i + q];
+      const float4 b = reinterpret_cast<const float4*>(m)[2 * i + q];
+      const float4 c = reinterpret_cast<const float4*>(v)[2 * i + q];
+      pv[4 * q] = a.x; pv[4 * q + 1] = a.y; pv[4 * q + 2] = a.z; pv[4 * q + 3] = a.w;
+      mv[4 * q] = b.x; mv[4 * q + 1] = b.y; mv[4 * q + 2] = b.z; mv[4 * q + 3] = b.w;
+      vv[4 * q] = c.x; vv[4 * q + 1] = c.y; vv[4 * q + 2] = c.z; vv[4 * q + 3] = c.w;
+    }
+    uint32_t out[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      adam_update(pv[2 * q], __uint_as_float(gw[q] << 16), mv[2 * q], vv[2 * q], h, bc1, bc2_sqrt);
+      adam_update(pv[2 * q + 1], __uint_as_float(gw[q] & 0xFFFF0000u), mv[2 * q + 1], vv[2 * q + 1], h, bc1, bc2_sqrt);
+      const __nv_bfloat162 r = __floats2bfloat162_rn(pv[2 * q], pv[2 * q + 1]);
+      out[q] = *reinterpret_cast<const uint32_t*>(&r);
+    }
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      reinterpret_cast<float4*>(master)[2 * i + q] = make_float4(pv[4 * q], pv[4 * q + 1], pv[4 * q + 2], pv[4 * q + 3]);
+      reinterpret_cast<float4*>(m)[2 * i + q] = make_float4(mv[4 * q], mv[4 * q + 1], mv[4 * q + 2], mv[4 * q + 3]);
+      reinterpret_cast<float4*>(v)[2 * i + q] = make_float4(vv[4 * q], vv[4 * q + 1], vv[4 * q + 2], vv[4 * q + 3]);
+    }
+    reinterpret_cast<uint4*>(p16)[i] = make_uint4(out[0], out[1], out[2], out[3]);
+  }
+  if (blockIdx.x == 0) {
+    for (size_t i = nvec * 8 + threadIdx.x; i < n; i += blockDim.x) {
+      float pf = master[i], mf = m[i], vf = v[i];
+      adam_update(pf, __bfloat162float(g16[i]), mf, vf, h, bc1, bc2_sqrt);
+      master[i] = pf; m[i] = mf; v[i] = vf;
+      p16[i] = __float2bfloat16_rn(pf);
+    }
+  }
+}
+
 __global__ void adam_advance_kernel(rtdc_adam_hyper* h) { h->step += 1; }
 __global__ void counter_advance_kernel(uint32_t* c, rtdc_sgd_hyper* h) {
   if (c) c[0] += 1u;
@@ -715,6 +768,19 @@ RTDC_API int rtdc_adam_step(float* p, const float* g, float* m, float* v, size_t
   if ((reinterpret_cast<uintptr_t>(p) & 15u) || (reinterpret_cast<uintptr_t>(g) & 15u) || (reinterpret_cast<uintptr_t>(m) & 15u) || (reinterpret_cast<uintptr_t>(v) & 15u))
     return fail(RTDC_ERR_ARG, "adam_step: arenas must be 16-byte aligned");
   adam_kernel<<<grid_for(n / 4 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, v, n, hyper_dev);
+  RTDC_CUDA_CHECK(cudaGetLastError());
+  return RTDC_OK;
+}
+
+RTDC_API int rtdc_adam_step_bf16(void* p_bf16, const void* g_bf16, float* master, float* m, float* v, size_t n,
+                                 const rtdc_adam_hyper* hyper_dev, void* stream) {
+  if (!p_bf16 || !g_bf16 || !master || !m || !v || !hyper_dev) return fail(RTDC_ERR_ARG, "adam_step_bf16: null pointer");
+  if (n == 0) return RTDC_OK;
+  const uintptr_t all = reinterpret_cast<uintptr_t>(p_bf16) | reinterpret_cast<uintptr_t>(g_bf16) | reinterpret_cast<uintptr_t>(master) |
+                        reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v);
+  if (all & 15u) return fail(RTDC_ERR_ARG, "adam_step_bf16: arenas must be 16-byte aligned");
+  adam_bf16_kernel<<<grid_for(n / 8 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<__nv_bfloat16*>(p_bf16), static_cast<const __nv_bfloat16*>(g_bf16), master, m, v, n, hyper_dev);
   RTDC_CUDA_CHECK(cudaGetLastError());
   return RTDC_OK;
 }

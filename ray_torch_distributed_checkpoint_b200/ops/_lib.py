@@ -95,6 +95,8 @@ def _declare(lib):
     lib.rtdc_sgd_step_advance_log.argtypes = [vp, vp, vp, sz, vp, vp, vp, vp, C.c_uint32, vp]
     lib.rtdc_sgd_step_advance_log.restype = i
     lib.rtdc_adam_step.argtypes = [vp, vp, vp, vp, sz, vp, vp]
+    lib.rtdc_adam_step_bf16.argtypes = [vp, vp, vp, vp, vp, sz, vp, vp]
+    lib.rtdc_adam_step_bf16.restype = i
     lib.rtdc_adam_advance.argtypes = [vp, vp]
     lib.rtdc_counter_advance.argtypes = [vp, vp, vp]
     for name in ("rtdc_gemm", "rtdc_gemm_plan", "rtdc_softmax_ce", "rtdc_colsum", "rtdc_u8_normalize", "rtdc_u8_affine",

@@ -243,9 +243,16 @@ class AdamState:
         self.dev.copy_(torch.frombuffer(bytearray(bytes(cur)), dtype=torch.uint8))
 
 
-def adam_step(p, g, m, v, state: AdamState, stream=None):
-    """Advance the device step counter, then one fused Adam/AdamW step over flat fp32 arenas."""
+def adam_step(p, g, m, v, state: AdamState, stream=None, master=None):
+    """Advance the device step counter, then one fused Adam/AdamW step over flat arenas: fp32 ``p`` / ``g``, or bf16 ``p`` /
+    ``g`` with an fp32 ``master`` copy of the parameters (``m`` / ``v`` are fp32 either way)."""
     lib = _lib.load()
     sp = _lib.stream_ptr(stream)
     _lib.check(lib.rtdc_adam_advance(state.dev.data_ptr(), sp))
+    if p.dtype == torch.bfloat16:
+        if master is None or master.dtype != torch.float32 or g.dtype != torch.bfloat16:
+            raise ValueError("bf16 parameters need bf16 gradients and an fp32 master copy")
+        _lib.check(lib.rtdc_adam_step_bf16(p.data_ptr(), g.data_ptr(), master.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(),
+                                           state.dev.data_ptr(), sp))
+        return
     _lib.check(lib.rtdc_adam_step(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), state.dev.data_ptr(), sp))

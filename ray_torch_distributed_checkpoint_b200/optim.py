@@ -171,8 +171,14 @@ class Adam(_FlatOptimizer):
                  decoupled_weight_decay: bool = False):
         super().__init__(model_or_params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
         self.decoupled = decoupled_weight_decay
-        self.m_arena = torch.zeros_like(self.p_arena)
-        self.v_arena = torch.zeros_like(self.p_arena)
+        # bf16 parameters (the GPT-2 / ResNet-50 configurations): moments and a master copy of the parameters in fp32, one fused
+        # kernel reads the bf16 gradient arena and rewrites the bf16 parameters from the master
+        self.bf16 = self.device.type == "cuda" and self.p_arena.dtype == torch.bfloat16
+        if self.bf16:
+            self.use_kernels = True
+            self.master = self.p_arena.float()
+        self.m_arena = torch.zeros_like(self.p_arena, dtype=torch.float32) if self.bf16 else torch.zeros_like(self.p_arena)
+        self.v_arena = torch.zeros_like(self.m_arena)
         self._steps = 0
         self.state_dev = ops.AdamState(self.device, lr, betas, eps, weight_decay, decoupled_weight_decay) if self.use_kernels else None
         self.param_groups = [dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay, amsgrad=False, maximize=False,
@@ -187,7 +193,8 @@ class Adam(_FlatOptimizer):
         if self.use_kernels:
             if g["lr"] != self.state_dev.host.lr:
                 self.state_dev.update(lr=g["lr"])
-            ops.adam_step(self.p_arena, self.g_arena, self.m_arena, self.v_arena, self.state_dev)
+            ops.adam_step(self.p_arena, self.g_arena, self.m_arena, self.v_arena, self.state_dev,
+                          master=self.master if self.bf16 else None)
             return
         b1, b2 = g["betas"]
         grad = self.g_arena

@@ -120,7 +120,8 @@ class DistributedDataParallel(nn.Module):
         self.param_arena = torch.zeros(total, dtype=self.dtype, device=dev)
         if use_symm:
             from .symm import SymmetricArena
-            self.symm = SymmetricArena(total * esize + 4096, device=dev, group=process_group)
+            buf_bytes = sum((b.numel() * b.element_size() + 511) // 512 * 512 for b in module.buffers()) + 1024
+            self.symm = SymmetricArena(total * esize + 4096 + buf_bytes, device=dev, group=process_group)
             goff, self.grad_arena = self.symm.alloc(total, self.dtype)
             self.comm = _SymmComm(self.symm, goff, esize, self.dtype, algo)
         else:
@@ -150,6 +151,22 @@ class DistributedDataParallel(nn.Module):
         self._ready = [0] * len(self.buckets)
         self._callback_queued = False
         self._hooks = [p.register_post_accumulate_grad_hook(self._make_hook(p)) for p in self._params]
+
+        # C4: module buffers (BatchNorm running statistics ...) live in ONE block of the symmetric arena, so that following
+        # rank 0 is one P2P broadcast kernel per forward instead of one collective per tensor
+        self._buf_block = None
+        bufs = [b for b in module.buffers() if b.numel() > 0]
+        if self.symm is not None and bufs:
+            start = None
+            with torch.no_grad():
+                for b in bufs:
+                    off, view = self.symm.alloc(b.numel(), b.dtype, align=16)
+                    start = off if start is None else start
+                    view = view.view(b.shape)
+                    view.copy_(b)
+                    b.data = view
+                    end = off + b.numel() * b.element_size()
+            self._buf_block = (start, end - start)
 
         # C2: every replica starts from rank 0's parameters (and buffers)
         self.comm.broadcast_(self.param_arena, src=0)
@@ -188,11 +205,14 @@ class DistributedDataParallel(nn.Module):
         self.comm.finish()
 
     def _sync_buffers(self):
-        bufs = [b for b in self.module.buffers() if b.numel() > 0]
-        if not bufs or self.world_size == 1:
+        if self.world_size == 1:
             return
-        for b in bufs:                       # C4: ResNet-style running stats follow rank 0
-            if b.is_floating_point() or b.dtype in (torch.int64, torch.int32):
+        if self._buf_block is not None:      # C4: the whole buffer block follows rank 0 with one NVLink broadcast kernel
+            off, nbytes = self._buf_block
+            self.symm.broadcast(off, nbytes, 0, self.symm.tensor(off, nbytes, torch.uint8))
+            return
+        for b in self.module.buffers():      # gloo workers (CPU): per tensor through torch.distributed
+            if b.numel() > 0 and (b.is_floating_point() or b.dtype in (torch.int64, torch.int32)):
                 dist.broadcast(b, src=0, group=self.process_group)
 
     # ------------------------------------------------------------------------------------------

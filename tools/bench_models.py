@@ -26,7 +26,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--algo", default="auto")
     ap.add_argument("--ckpt-every", type=int, default=0, help="async checkpoint every N steps (ours) / torch.save (torch)")
+    ap.add_argument("--linear", choices=["ours", "torch"], default=None, help="gpt2: nn.Linear on the repo's bf16 tcgen05 GEMM (default with --ddp ours) or cuBLAS")
+    ap.add_argument("--opt", choices=["ours", "torch"], default=None, help="gpt2: the repo's fused bf16 AdamW kernel over the flat arena (default with --ddp ours) or torch's fused AdamW")
     args = ap.parse_args()
+    args.linear = args.linear or ("ours" if args.ddp == "ours" else "torch")
+    args.opt = args.opt or ("ours" if args.ddp == "ours" else "torch")
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -40,22 +44,29 @@ def main():
         x = torch.randn(B, 3, 224, 224, device=dev, dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
         y = torch.randint(0, 1000, (B,), device=dev)
         loss_of = lambda m: torch.nn.functional.cross_entropy(m(x).float(), y)
-        opt_cls = lambda p: torch.optim.SGD(p, lr=0.1, momentum=0.9)
+        opt_cls = lambda m: torch.optim.SGD(m.parameters(), lr=0.1, momentum=0.9)
         per_sample = 1
     else:
         B = args.batch or 16
         model = GPT2(GPT2Config()).to(dev, dtype=torch.bfloat16)
+        if args.linear == "ours":
+            from ray_torch_distributed_checkpoint_b200.ops import use_bf16_linears
+            use_bf16_linears(model)                      # 48 Linear layers: forward, dgrad, wgrad on csrc/gemm_bf16.cu
         idx = torch.randint(0, 50257, (B, 1024), device=dev)
         tgt = torch.randint(0, 50257, (B, 1024), device=dev)
         loss_of = lambda m: m(idx, tgt)
-        opt_cls = lambda p: torch.optim.AdamW(p, lr=3e-4, fused=True)
+        if args.opt == "ours":
+            from ray_torch_distributed_checkpoint_b200.optim import AdamW
+            opt_cls = lambda m: AdamW(m, lr=3e-4)        # adam_bf16_kernel: fp32 master + moments, one launch over the arena
+        else:
+            opt_cls = lambda m: torch.optim.AdamW(m.parameters(), lr=3e-4, fused=True)
         per_sample = 1024
     if world > 1:
         if args.ddp == "ours":
             model = DistributedDataParallel(model, device=dev, algo=args.algo)
         else:
             model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True)
-    opt = opt_cls(model.parameters())
+    opt = opt_cls(model)
     ckpt = None
     if args.ckpt_every and rank == 0 and args.ddp == "ours":
         from ray_torch_distributed_checkpoint_b200.ckpt import AsyncCheckpointer
@@ -91,16 +102,23 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    # time to durable: until the last checkpoint's files are published (the asynchronous writer is still busy when the last
+    # step's kernels finish; torch.save in the stock arm is synchronous, so for it both numbers coincide)
+    import time
+    t_wall = time.perf_counter()
     if ckpt is not None:
         ckpt.wait()
+    durable_extra_ms = (time.perf_counter() - t_wall) * 1e3
+    if world > 1:
+        t = torch.tensor([ms, durable_extra_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, durable_extra_ms = float(t[0].item()), float(t[1].item())
     if rank == 0:
         print(json.dumps({"model": args.model, "ddp": args.ddp, "n_gpus": world, "batch_per_gpu": B, "steps": args.steps,
                           "ms_per_step": round(ms / args.steps, 3), "samples_per_s": round(B * world * args.steps / (ms / 1e3), 1),
                           "tokens_per_s": round(B * world * per_sample * args.steps / (ms / 1e3), 1) if per_sample > 1 else None,
+                          "ms_per_step_until_durable": round((ms + durable_extra_ms) / args.steps, 3),
+                          "linear": args.linear if args.model == "gpt2" else "torch", "optimizer": args.opt if args.model == "gpt2" else "torch",
                           "ckpt_every": args.ckpt_every, "loss": round(float(loss), 4), "dtype": "bf16"}), flush=True)
     if world > 1:
         dist.barrier()
