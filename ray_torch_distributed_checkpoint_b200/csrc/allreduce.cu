@@ -427,7 +427,10 @@ RTDC_API int rtdc_symm_all_reduce(void* handle, size_t offset, size_t count, int
   const size_t nvec = count * esize / 16;
   if (algo == 0) {
     const size_t bytes = count * esize;
-    if (info.multicast_ptr && bytes >= (1u << 20) && info.world > 2) algo = 3;   // two ranks: the P2P two-shot is quicker (20 vs 27 us at 1.6 MB)
+    // measured on 8 B200 (tools/bench_allreduce.py, profiles/): the unrolled P2P two-shot wins up to tens of MB (2.68 MB: 24.8 vs
+    // 25.9 us NVLS vs 40.3 us NCCL; 27 MiB: 88 vs 99 vs 117 us); the switch reduction wins once the message is bandwidth-bound
+    // (98 MiB: 264 us NVLS vs 292 us two-shot vs 321 us NCCL)
+    if (info.multicast_ptr && bytes >= (64u << 20) && info.world > 2) algo = 3;
     else algo = 2;
   }
   if (algo == 3 && !info.multicast_ptr) return fail(RTDC_ERR_ARG, "all_reduce: NVLS requested but multicast is not available");
@@ -493,7 +496,8 @@ RTDC_API int rtdc_symm_sgd_step(void* handle, size_t g_offset, size_t p_offset, 
     return fail(RTDC_ERR_LIMIT, "symm_sgd_step: an arena exceeds the symmetric buffer (%zu bytes)", info.bytes);
   if (loss_log_slots & (loss_log_slots - 1)) return fail(RTDC_ERR_ARG, "symm_sgd_step: loss_log_slots must be a power of two");
   if (count == 0) return RTDC_OK;
-  if (algo == 0) algo = (info.multicast_ptr && info.world > 2) ? 3 : 2;
+  // latency-bound at the MLP's 2.68 MB: peer loads + peer stores (24.3 us at 8 GPUs) beat the multimem path (28.9 us)
+  if (algo == 0) algo = (info.multicast_ptr && info.world > 2 && bytes >= (64u << 20)) ? 3 : 2;
   if (algo == 3 && !info.multicast_ptr) return fail(RTDC_ERR_ARG, "symm_sgd_step: NVLS requested but multicast is not available");
   if (algo != 2 && algo != 3) return fail(RTDC_ERR_ARG, "symm_sgd_step: algo must be 0 (auto), 2 (P2P) or 3 (NVLS)");
   const size_t nvec = count / 4;

@@ -422,7 +422,7 @@ class U8BatchLoader:
                  world: int = 1, rank: int = 0, seed: int = 0, drop_last: bool = True, normalize: bool = False,
                  mean: float = 0.5, std: float = 0.5, lookahead: int = 2, prefetch_next_epoch: bool = True,
                  wrap: bool = False, timed: bool = False, transfer: str = "auto", shuffle_block: int = 2048,
-                 resident_max_bytes: int = 4 << 30):
+                 resident_max_bytes: int = 4 << 30, resident_host_perm_max_rows: int = 250_000):
         assert images_u8.dtype == torch.uint8 and labels.dtype in (torch.int64, torch.uint8)
         self.prefetch_next_epoch = prefetch_next_epoch
         self.image_shape = tuple(images_u8.shape[1:]) if images_u8.dim() > 2 else (images_u8.shape[1],)
@@ -455,6 +455,7 @@ class U8BatchLoader:
         self._closed = False
         self._iterated_epoch = None
         self._epoch_copies_done = [None, None]
+        self._device_perm = False
 
         if transfer == "stream":
             self.sampler = BlockSampler(n_rows, shuffle_block, world, rank, shuffle=shuffle, seed=seed)
@@ -476,6 +477,9 @@ class U8BatchLoader:
             if transfer == "resident":
                 self.images = images.contiguous().to(self.device)            # the one upload of the pixels
                 self.labels = labels.contiguous().to(self.device)
+                # torch.randperm on one host core costs ~12 ns per row: fine for FashionMNIST (0.7 ms), not for millions of rows
+                # per epoch, where the permutation is drawn on the GPU instead
+                self._device_perm = shuffle and n_rows > resident_host_perm_max_rows
                 self._host_idx = [torch.empty(n, dtype=torch.int32, pin_memory=True) for _ in range(2)]
                 self._dev_idx = [torch.empty(n, dtype=torch.int32, device=self.device) for _ in range(2)]
                 self.h2d_bytes_per_batch = self.batch_size * 4                # the batch's indices
@@ -528,6 +532,8 @@ class U8BatchLoader:
                 G = self.sampler.block
                 torch.index_select(self.labels.view(-1), 0, (starts[:, None] + torch.arange(G)[None, :]).reshape(-1), out=self._host_y[slot])
                 return starts
+            if self.transfer == "resident" and self._device_perm:
+                return "device"                     # the permutation itself is drawn on the GPU in _epoch_resident
             idx = self.sampler.indices_tensor()
         finally:
             self.sampler.set_epoch(old_epoch)
@@ -596,11 +602,26 @@ class U8BatchLoader:
         else:
             self._dev_y[bi][:hi - lo].copy_(hy[lo:hi], non_blocking=True)
 
+    def _device_indices(self, epoch: int, slot: int):
+        """This rank's shard of the epoch's permutation, drawn on the GPU (same seed on every rank => same permutation; same
+        pad-by-wrapping and stride-by-rank arithmetic as DistributedSampler, but not torch's CPU random stream)."""
+        sm = self.sampler
+        g = torch.Generator(device=self.device)
+        g.manual_seed(sm.seed + epoch)
+        perm = torch.randperm(sm.n, device=self.device, generator=g) if sm.shuffle else torch.arange(sm.n, device=self.device)
+        pad = sm.total_size - sm.n
+        if pad > 0:
+            perm = torch.cat([perm] + [perm] * (pad // sm.n) + [perm[:pad % sm.n]])
+        self._dev_idx[slot].copy_(perm[sm.rank:sm.total_size:sm.num_replicas])
+
     def _epoch_resident(self, epoch: int):
         from ..ops import u8_gather_rows
-        slot, _ = self._take_plan(epoch)
+        slot, plan = self._take_plan(epoch)
         with torch.cuda.stream(self.copy_stream):
-            self._dev_idx[slot].copy_(self._host_idx[slot], non_blocking=True)
+            if plan == "device":
+                self._device_indices(epoch, slot)
+            else:
+                self._dev_idx[slot].copy_(self._host_idx[slot], non_blocking=True)
         idx = self._dev_idx[slot]
 
         def fill(bi, lo, hi):

@@ -46,7 +46,17 @@ def main(payload_path: str) -> int:
                            storage.trial_path, storage, use_gpu, payload.get("metadata"))
         session = _Session(ctx, link, payload.get("start_checkpoint"), payload.get("start_index", 0))
         _set_session(session)
+        prof_path = os.environ.get("RTDC_WORKER_CPROFILE")           # host-side profile of the training function, per rank
+        if prof_path:
+            import cProfile
+            import pstats
+            prof = cProfile.Profile()
+            prof.enable()
         _call_train_fn(payload["fn"], payload["config"])
+        if prof_path:
+            prof.disable()
+            with open(f"{prof_path}.{rank}", "w") as f:
+                pstats.Stats(prof, stream=f).sort_stats("cumulative").print_stats(70)
         session.drain()
         if use_gpu:
             torch.cuda.synchronize()

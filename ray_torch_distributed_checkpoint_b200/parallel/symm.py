@@ -140,8 +140,8 @@ class SymmetricArena:
         a = _ALGO_NAMES[algo] if isinstance(algo, str) else int(algo)
         if a == ALGO_NVLS and not self.has_multicast:
             raise RuntimeError("NVLS requested but multicast is unavailable on this system")
-        if a == ALGO_AUTO:
-            a = ALGO_NVLS if (self.has_multicast and self.world > 2) else ALGO_TWO_SHOT
+        if a == ALGO_AUTO and not self.has_multicast:
+            a = ALGO_TWO_SHOT                       # else the library picks by size (P2P below 64 MiB, see csrc/allreduce.cu)
         if loss_log is not None and not loss_log.is_pinned():
             raise ValueError("loss_log must be pinned host memory")
         _lib.check(self.lib.rtdc_symm_sgd_step(self.handle, g_offset, p_offset, m_offset, numel, a, state.dev.data_ptr(),

@@ -126,7 +126,11 @@ def check_engine(rank, world, dev):
     from ray_torch_distributed_checkpoint_b200.parallel.engine import MLPTrainEngine
     B = 512
     finals, moms = {}, {}
-    modes = [("fused", "auto"), ("fused", "two_shot"), ("merged", "auto"), ("bucketed", "auto")]
+    from ray_torch_distributed_checkpoint_b200.parallel.symm import SymmetricArena
+    probe = SymmetricArena(1 << 20, device=dev)
+    has_mc = probe.has_multicast
+    probe.close()
+    modes = [("fused", "auto"), ("fused", "two_shot")] + ([("fused", "nvls")] if has_mc else []) + [("merged", "auto"), ("bucketed", "auto")]
     for mode, algo in modes:
         torch.manual_seed(3 + rank)
         eng = MLPTrainEngine(NeuralNetwork(), batch_size=B, lr=0.05, device=dev, seed=11, ar_mode=mode, algo=algo)
