@@ -211,3 +211,28 @@ def test_loader_transfer_modes_agree_with_their_samplers():
     # no shuffle: storage order
     ld = U8BatchLoader(ds.data, ds.targets, 400, "cuda", shuffle=False, drop_last=False, transfer="stream", shuffle_block=128)
     assert torch.equal(torch.cat([y.cpu() for _, y in ld])[:1000 - 1000 % 128], ds.targets[:1000 - 1000 % 128])
+
+
+def test_async_snapshot_of_arena_views_is_exact():
+    from ray_torch_distributed_checkpoint_b200.ckpt import AsyncCheckpointer
+    from ray_torch_distributed_checkpoint_b200.nn import CrossEntropyLoss
+    from ray_torch_distributed_checkpoint_b200.optim import SGD
+    model = _prepared(seed=5)
+    opt = SGD(model, lr=0.05, momentum=0.9)
+    x = torch.randn(128, 1, 28, 28, device="cuda"); y = torch.randint(0, 10, (128,), device="cuda")
+    loss = CrossEntropyLoss()(model(x), y); loss.backward(); opt.step()
+    state = {"model_state_dict": model.state_dict(), "optimizer_state_dict": opt.state_dict(), "extra": torch.arange(5, device="cuda"), "epoch": 3}
+    want = {k: v.clone() for k, v in state["model_state_dict"].items()}
+    want_m = [v["momentum_buffer"].clone() for v in state["optimizer_state_dict"]["state"].values()]
+    ck = AsyncCheckpointer(torch.device("cuda"))
+    cpu_state, _slot = ck.snapshot(state)
+    loss = CrossEntropyLoss()(model(x), y); loss.backward(); opt.step()          # the live arenas move on; the snapshot must not
+    got = cpu_state()
+    assert got["epoch"] == 3 and torch.equal(got["extra"], torch.arange(5))
+    for k, v in want.items():
+        assert not got["model_state_dict"][k].is_cuda and torch.equal(got["model_state_dict"][k], v.cpu()), k
+    for i, v in enumerate(want_m):
+        assert torch.equal(got["optimizer_state_dict"]["state"][i]["momentum_buffer"], v.cpu())
+    assert ck.stats["snapshots"] == 1
+    ck.close()
+    model.close()
