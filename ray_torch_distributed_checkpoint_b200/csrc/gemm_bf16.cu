@@ -60,6 +60,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar[2], tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_slot;
+  __shared__ __align__(16) float bias_s[MAX_BN];
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);   // warp-uniform for the compiler
   const int lane = threadIdx.x & 31;
@@ -153,42 +154,77 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else {
     // ------------------------------------------------------------------ epilogue: TMEM -> registers -> global
+    // The four warps first stage the tile's bias slice as fp32 in shared memory (one coalesced pass instead of 32 scalar
+    // loads per thread and chunk), then walk the accumulator 32 columns at a time with the next chunk's tcgen05.ld already
+    // in flight while the current one is converted and stored.
     const int q = warp & 3;                                 // this warp's TMEM lane quarter
+    const int et = threadIdx.x - 64;                        // 0..127 among the epilogue threads
     int j = 0;
     for (int u = blockIdx.x; u < total_units; u += gridDim.x, ++j) {
       const int tile = u / p.splits;
       const int m0 = (tile % p.m_tiles) * BM, n0 = (tile / p.m_tiles) * p.bn;
       const int buf = j & 1;
+      const int n_valid = min(p.bn, p.N - n0);
+      const bool has_bias = p.bias != nullptr;
+      if (has_bias) {
+        named_bar_sync(1, 128);                             // everyone is done reading the previous tile's slice
+        for (int i = et; i < p.bn; i += 128) {
+          float bv = 0.f;
+          if (i < n_valid)
+            bv = p.bias_fp32 ? __ldg(static_cast<const float*>(p.bias) + n0 + i)
+                             : __bfloat162float(static_cast<const __nv_bfloat16*>(p.bias)[n0 + i]);
+          bias_s[i] = bv;
+        }
+        named_bar_sync(1, 128);
+      }
       mbar_wait(&tmem_full_bar[buf], (j >> 1) & 1);
       tcgen05_fence_after();
       const int row = m0 + q * 32 + lane;
       const uint32_t taddr = tmem_base + static_cast<uint32_t>(buf) * MAX_BN + (static_cast<uint32_t>(q * 32) << 16);
-      const int n_valid = min(p.bn, p.N - n0);
+      const int n_chunks = (n_valid + 31) / 32;
       uint32_t r[32];
-      for (int c = 0; c * 32 < n_valid; ++c) {
-        tmem_ld_32x32(taddr + c * 32, r);
+      if (n_chunks > 0) tmem_ld_32x32(taddr, r);
+      for (int c = 0; c < n_chunks; ++c) {
         tmem_ld_wait();
-        const int col0 = n0 + c * 32;
-        if (row < p.M) {
-          float v[32];
+        float v[32];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            float x = __uint_as_float(r[i]) * p.alpha;
-            if (p.bias != nullptr && col0 + i < p.N)
-              x += p.bias_fp32 ? __ldg(static_cast<const float*>(p.bias) + col0 + i)
-                               : __bfloat162float(static_cast<const __nv_bfloat16*>(p.bias)[col0 + i]);
-            v[i] = apply_act(x, p.act);
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+        if (c + 1 < n_chunks) tmem_ld_32x32(taddr + (c + 1) * 32, r);     // in flight while this chunk is processed
+        const int col0 = n0 + c * 32;
+        if (has_bias) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 bq = *reinterpret_cast<const float4*>(&bias_s[c * 32 + 4 * i]);
+            v[4 * i] += bq.x; v[4 * i + 1] += bq.y; v[4 * i + 2] += bq.z; v[4 * i + 3] += bq.w;
           }
+        }
+        if (p.act != 0) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = apply_act(v[i], p.act);
+        }
+        if (row < p.M) {
           const int ncol = min(32, p.N - col0);
           if (p.out_fp32) {
             float* dst = static_cast<float*>(p.out) + static_cast<size_t>(row) * p.ldo + col0;
+            const bool vec = ncol == 32 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
             if (p.splits > 1) {
-              for (int i = 0; i < ncol; ++i) atomicAdd(dst + i, v[i]);
-            } else if (ncol == 32 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+              if (vec) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * i), "f"(v[4 * i]), "f"(v[4 * i + 1]),
+                               "f"(v[4 * i + 2]), "f"(v[4 * i + 3]) : "memory");
+              } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  if (i < ncol) atomicAdd(dst + i, v[i]);
+              }
+            } else if (vec) {
 #pragma unroll
               for (int i = 0; i < 8; ++i) reinterpret_cast<float4*>(dst)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
             } else {
-              for (int i = 0; i < ncol; ++i) dst[i] = v[i];
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (i < ncol) dst[i] = v[i];
             }
           } else {
             __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(p.out) + static_cast<size_t>(row) * p.ldo + col0;
@@ -204,7 +240,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 reinterpret_cast<uint4*>(dst)[i] = make_uint4(w[0], w[1], w[2], w[3]);
               }
             } else {
-              for (int i = 0; i < ncol; ++i) dst[i] = __float2bfloat16_rn(v[i]);
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (i < ncol) dst[i] = __float2bfloat16_rn(v[i]);
             }
           }
         }

@@ -81,17 +81,24 @@ class _Session:
     def _do_report(self, idx: int, metrics: Dict[str, Any], checkpoint):
         ctx = self.context
         persisted_path = None
+        t0 = time.time()
         if checkpoint is not None and hasattr(checkpoint, "result") and not isinstance(checkpoint, Checkpoint):
             checkpoint = checkpoint.result()          # ckpt.PendingCheckpoint: wait for the writer thread
+        t1 = time.time()
         if checkpoint is not None:
             storage = ctx.get_storage()
-            t0 = time.time()
             with checkpoint.as_directory() as src:
                 persisted_path = storage.persist_checkpoint_files(src, idx, ctx.get_world_rank())
             metrics = dict(metrics)
-            metrics.setdefault("_checkpoint_persist_s", round(time.time() - t0, 6))
+            metrics.setdefault("_checkpoint_persist_s", round(time.time() - t1, 6))
+        t2 = time.time()
         # blocks until every rank has reported this index and the bookkeeping is done (C5 barrier)
         self.link.report(rank=ctx.get_world_rank(), index=idx, metrics=metrics, checkpoint_path=persisted_path)
+        t3 = time.time()
+        self.phase_s = [a + b for a, b in zip(getattr(self, "phase_s", [0.0, 0.0, 0.0]), (t1 - t0, t2 - t1, t3 - t2))]
+        if os.environ.get("RTDC_PROFILE_EPOCHS"):
+            print(f"[rtdc] rank {ctx.get_world_rank()} report {idx}: wait for the checkpoint writer {(t1 - t0) * 1e3:.2f} ms, persist "
+                  f"{(t2 - t1) * 1e3:.2f} ms, driver round trip {(t3 - t2) * 1e3:.2f} ms", flush=True)
         if self.link.any_checkpoint(idx):
             self.latest_checkpoint = Checkpoint.from_directory(ctx.get_storage().checkpoint_path(idx))
         _maybe_inject_fault(ctx.get_world_rank(), idx + 1)

@@ -152,7 +152,10 @@ class StorageContext:
                 if rank != 0 and os.path.exists(dst):
                     continue
                 tmp = os.path.join(out_root, f".{name}.rank{rank}.{os.getpid()}.tmp")
-                shutil.copyfile(src, tmp)
+                try:
+                    os.link(src, tmp)                 # same filesystem: publishing a checkpoint file costs no copy
+                except OSError:
+                    shutil.copyfile(src, tmp)
                 if rank == 0:
                     os.replace(tmp, dst)
                 else:
