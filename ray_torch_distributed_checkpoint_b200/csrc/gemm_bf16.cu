@@ -312,7 +312,9 @@ template <bool A_MN, bool B_MN>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int grid, size_t smem, cudaStream_t st) {
   static bool configured = false;
   if (!configured) {
-    RTDC_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 1024));
+    // the largest plan: four stages of a 128 x 64 A tile and a 256 x 64 B tile, plus the 1 KB alignment slack
+    RTDC_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         STAGES * (A_BYTES + MAX_BN * BK * 2) + 1024));
     configured = true;
   }
   gemm_bf16_kernel<A_MN, B_MN><<<grid, NUM_THREADS, smem, st>>>(ta, tb, p);

@@ -1,5 +1,8 @@
 """Run one kernel case a few times (for ncu / sanitizer captures). Usage:
 python tools/profile_case.py <fwd1|fwd2|dgrad2|wgrad1|wgrad2> <precision> [batch] [iters]"""
+import os as _os, sys as _sys
+_sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
+
 import sys
 
 import torch

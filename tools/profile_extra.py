@@ -2,6 +2,9 @@
 shapes (forward / dgrad / wgrad), the resident loader's gather kernel, the evaluation loss kernel, the activation backward,
 the bf16 AdamW kernel, and the single-rank instances of the collective kernels (two-shot, fused optimizer step: same code,
 no peers)."""
+import os as _os, sys as _sys
+_sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
+
 import torch
 
 from ray_torch_distributed_checkpoint_b200 import ops

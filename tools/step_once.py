@@ -1,4 +1,7 @@
 """A few training steps of the engine without CUDA graphs (so ncu sees plain kernel launches)."""
+import os as _os, sys as _sys
+_sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
+
 import sys
 import torch
 from ray_torch_distributed_checkpoint_b200.models import NeuralNetwork
