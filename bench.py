@@ -187,6 +187,17 @@ def _blocks(per_rank, warm_epochs, R, S):
         lo, hi = (warm_epochs + r) * S, (warm_epochs + r + 1) * S
         dev_blocks.append(max(sum(t["device_ms"][lo:hi]) for t in per_rank))
         e2e_blocks.append(max(t["end_ms_since_first_begin"][hi - 1] - t["end_ms_since_first_begin"][lo - 1] for t in per_rank))
+    # where the end-to-end time beyond the steps themselves goes (rank 0): device-time gaps between a step's end stamp and the
+    # next step's begin stamp inside an epoch, and across the epoch boundary (validation, checkpoint, report, next epoch's start)
+    t0 = per_rank[0]
+    bg, en = t0["begin_ms_since_first_begin"], t0["end_ms_since_first_begin"]
+    intra, boundary = [], []
+    for r in range(R):
+        lo, hi = (warm_epochs + r) * S, (warm_epochs + r + 1) * S
+        intra.append(sum(bg[i + 1] - en[i] for i in range(lo, hi - 1)))
+        boundary.append(bg[lo] - en[lo - 1])
+    _blocks.breakdown = {"intra_epoch_gap_ms_per_epoch": round(statistics.median(intra), 3),
+                         "epoch_boundary_ms": round(statistics.median(boundary), 3)}
     host_gaps = []                    # host side: time between consecutive batches handed to the loop, worst rank's median
     for t in per_rank:
         hb = t["host_begin_s"]
@@ -225,6 +236,7 @@ def run_ours(args):
         if rank == 0:
             dev_blocks, e2e_blocks, host_ms = _blocks(per_rank, warm_epochs, R, S)
             runs[transfer] = dict(dev=_median_block(dev_blocks), e2e=_median_block(e2e_blocks), host_ms=host_ms, clocks=clocks, wall=wall,
+                                  breakdown=dict(_blocks.breakdown),
                                   extra=per_rank[0].get("extra", {}),
                                   metrics={k: v for k, v in (getattr(result, "metrics", None) or {}).items() if not str(k).startswith("_")})
     if rank == 0:
@@ -244,7 +256,7 @@ def run_ours(args):
                     "ms_per_step_min": round(e_min / K, 4), "ms_per_step_max": round(e_max / K, 4),
                     "device_ms_per_step": round(run["dev"][0] / K, 4), "host_ms_per_step": round(run["host_ms"], 4),
                     "h2d_bytes_per_step": int(run["extra"].get("h2d_bytes_per_step", 0)), "d2h_bytes_per_step": 4,
-                    "input_transfer": name}
+                    "input_transfer": name, **run["breakdown"]}
 
         e2e = e2e_dict(e_run, e_name)
         e2e.update({"window": "end of the previous epoch's last step -> end of this epoch's last step: validation, checkpoint snapshot, "

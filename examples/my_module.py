@@ -162,8 +162,11 @@ def train_func_per_worker(config: Dict):
             names = [LATEST_CHECKPOINT_FILENAME]
             if val_loss < best_val_loss:
                 names.append(BEST_CHECKPOINT_FILENAME)
-            pending = checkpointer.save(_checkpoint_state(epoch, model, optimizer, val_losses, val_acc),
-                                        tempfile.mkdtemp(prefix="rtdc_ckpt_"), names)
+            state = _checkpoint_state(epoch, model, optimizer, val_losses, val_acc)
+            t2b = time.time()
+            pending = checkpointer.save(state, tempfile.mkdtemp(prefix="rtdc_ckpt_"), names)
+            if os.environ.get("RTDC_PROFILE_EPOCHS"):
+                print(f"[my_module] state_dict {(t2b - t2) * 1e3:.2f} ms, save() {(time.time() - t2b) * 1e3:.2f} ms", flush=True)
         best_val_loss = min(best_val_loss, val_loss)
         t3 = time.time()
         # every rank reports; the checkpoint write, its persistence and the cross-worker barrier finish in

@@ -203,7 +203,9 @@ class AsyncCheckpointer:
             n = t.numel() * t.element_size()
             offsets[k] = (total, n)
             total += _align(n)
+        t_plan = time.perf_counter()
         slot = self._acquire_slot(total)
+        t_slot = time.perf_counter()
         done_event = None
         if self.is_cuda:
             main = torch.cuda.current_stream(self.device)
@@ -253,6 +255,9 @@ class AsyncCheckpointer:
         self.stats["snapshots"] += 1
         self.stats["bytes"] += total
         self.stats["critical_path_s"] += time.perf_counter() - t0
+        if os.environ.get("RTDC_PROFILE_EPOCHS"):
+            print(f"[rtdc] snapshot: plan {(t_plan - t0) * 1e3:.2f} ms, wait for a free slot {(t_slot - t_plan) * 1e3:.2f} ms, enqueue copies "
+                  f"{(time.perf_counter() - t_slot) * 1e3:.2f} ms", flush=True)
         return cpu_state, slot
 
     def save(self, state: Any, directory: str, filenames) -> PendingCheckpoint:

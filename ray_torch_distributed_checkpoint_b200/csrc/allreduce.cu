@@ -265,6 +265,8 @@ template <int WORLD, bool NVLS>
 __global__ void __launch_bounds__(AR_THREADS)
 sgd_fused_kernel(SymmView sv, size_t g_off, size_t p_off, size_t m_off, size_t nvec_total, float inv_world, rtdc_sgd_hyper* hp,
                  uint32_t* step_counter, const float* loss, float* loss_log, uint32_t log_mask) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int U = NVLS ? AR_UNROLL : P2PUnroll<WORLD>::value;
   const unsigned int e = epoch_begin(sv);
   const rtdc_sgd_hyper h = *hp;

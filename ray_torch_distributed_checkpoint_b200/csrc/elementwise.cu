@@ -194,6 +194,8 @@ constexpr int CS_MAX_SLABS = 64;   // (the built-in scratch of rtdc_colsum_noall
 __global__ void __launch_bounds__(CS_THREADS)
 colsum_kernel(const float* __restrict__ x, int ld, int rows, int cols, float* __restrict__ out, float* partial,
               unsigned int* counters, int rows_per_slab) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float4 s_acc[CS_THREADS / 32][32];
   __shared__ unsigned int s_last;
   const int cg = blockIdx.x, slab = blockIdx.y;
@@ -312,6 +314,8 @@ u8_normalize_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst, si
 __global__ void __launch_bounds__(256)
 sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, size_t n,
            rtdc_sgd_hyper* hp, uint32_t* step_counter, int advance, const float* loss, float* loss_log, uint32_t log_mask) {
+  pdl_launch_dependents();
+  pdl_wait();
   const rtdc_sgd_hyper h = *hp;
   const size_t nvec = n / 4;
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
@@ -558,8 +562,8 @@ RTDC_API int rtdc_colsum(const float* x, int ld, int rows, int cols, float* out,
   if (static_cast<size_t>(cg) * 4 > CS_COUNTER_BYTES) return fail(RTDC_ERR_LIMIT, "colsum supports at most %zu columns", CS_COUNTER_BYTES / 4 * CS_COLS);
   unsigned int* counters = static_cast<unsigned int*>(scratch);
   float* partial = reinterpret_cast<float*>(static_cast<uint8_t*>(scratch) + CS_COUNTER_BYTES);
-  colsum_kernel<<<dim3(cg, slabs), CS_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x, ld, rows, cols, out, partial, counters, rps);
-  RTDC_CUDA_CHECK(cudaGetLastError());
+  RTDC_CUDA_CHECK(launch_pdl(colsum_kernel, dim3(cg, slabs), dim3(CS_THREADS), 0, static_cast<cudaStream_t>(stream), x, ld, rows, cols, out, partial,
+                             counters, rps));
   return RTDC_OK;
 }
 
@@ -742,9 +746,8 @@ static int sgd_launch(float* p, const float* g, float* m, size_t n, rtdc_sgd_hyp
   if (n == 0) return RTDC_OK;
   if ((reinterpret_cast<uintptr_t>(p) & 15u) || (reinterpret_cast<uintptr_t>(g) & 15u) || (reinterpret_cast<uintptr_t>(m) & 15u))
     return fail(RTDC_ERR_ARG, "sgd_step: arenas must be 16-byte aligned");
-  sgd_kernel<<<grid_for(n / 4 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, n, hyper_dev, counter, advance, loss,
-                                                                                        log_slots ? loss_log : nullptr, log_slots ? log_slots - 1 : 0);
-  RTDC_CUDA_CHECK(cudaGetLastError());
+  RTDC_CUDA_CHECK(launch_pdl(sgd_kernel, dim3(grid_for(n / 4 + 1, 256, 8)), dim3(256), 0, static_cast<cudaStream_t>(stream), p, g, m, n, hyper_dev,
+                             counter, advance, loss, log_slots ? loss_log : nullptr, log_slots ? log_slots - 1 : 0u));
   return RTDC_OK;
 }
 

@@ -361,6 +361,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmA3,
                  const __grid_constant__ CUtensorMap tmB3, const GemmParams p) {
   extern __shared__ uint8_t smem_dyn[];
+  pdl_launch_dependents();
   __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t ready_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
@@ -404,6 +405,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
+  pdl_wait();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_slot, 0);
   long long* stamps = p.dbg_times ? p.dbg_times + static_cast<size_t>(blockIdx.x) * 8 : nullptr;
   if (stamps && threadIdx.x == 0) { stamps[0] = clock64(); stamps[7] = static_cast<long long>(global_timer_ns()); }
@@ -673,6 +675,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
                         const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmA3,
                         const __grid_constant__ CUtensorMap tmB3, const GemmParams p) {
   extern __shared__ uint8_t smem_dyn[];
+  pdl_launch_dependents();
   __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t ready_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
@@ -721,6 +724,7 @@ gemm_tf32x3_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
   __syncthreads();
   cluster_sync_all();   // the peer's barriers are initialised before anybody arrives on them remotely
   tcgen05_fence_after();
+  pdl_wait();           // everything above ran beside the previous kernel's tail; its results are needed from here on
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_slot, 0);
 
   const int total_units = p.total_units;
@@ -975,6 +979,8 @@ __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const float* __restrict__ scratch, int splits_full, int splits_last, int n_tiles, int m_tiles, int bn, int M, int N,
                      int n_store, float* __restrict__ out, int ldo, const float* __restrict__ bias, int relu, float alpha,
                      const float* __restrict__ row_bias, float row_bias_scale) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int chunks = (bn + 31) / 32;
   const int tile = blockIdx.x / chunks, c = blockIdx.x % chunks;
   const int m_tile = tile % m_tiles, n_tile = tile / m_tiles;
@@ -1243,8 +1249,7 @@ static int launch_2cta_bk(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   RTDC_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT - STATIC_SMEM_RESERVE));
   const int units = gp.total_units;
   const int pairs = units < num_sms() / 2 ? units : num_sms() / 2;   // persistent: one CTA pair per TPC
-  kern<<<2 * pairs, NUM_THREADS, pl.smem, st>>>(ta, tb, to, ta3, tb3, gp);
-  RTDC_CUDA_CHECK(cudaGetLastError());
+  RTDC_CUDA_CHECK(launch_pdl(kern, dim3(2 * pairs), dim3(NUM_THREADS), pl.smem, st, ta, tb, to, ta3, tb3, gp));
   return RTDC_OK;
 }
 
@@ -1262,8 +1267,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
   RTDC_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT - STATIC_SMEM_RESERVE));
   const int units = gp.total_units;
   const int grid = units < num_sms() ? units : num_sms();   // persistent: one CTA per SM walks the work units
-  kern<<<grid, NUM_THREADS, pl.smem, st>>>(ta, tb, to, ta3, tb3, gp);
-  RTDC_CUDA_CHECK(cudaGetLastError());
+  RTDC_CUDA_CHECK(launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), pl.smem, st, ta, tb, to, ta3, tb3, gp));
   return RTDC_OK;
 }
 
@@ -1395,9 +1399,8 @@ RTDC_API int rtdc_gemm(const rtdc_gemm_desc* d, void* stream) {
   if (rc != RTDC_OK) return rc;
   if (pl.splits > 1) {
     dim3 grid(pl.m_tiles * pl.n_tiles * ((pl.bn + 31) / 32), BM / 32);
-    splitk_reduce_kernel<<<grid, 256, 0, st>>>(gp.scratch, pl.splits, pl.splits_last, pl.n_tiles, pl.m_tiles, pl.bn, d->M, d->N, n_store, d->out, d->ldo,
-                                              d->bias, d->relu, gp.alpha, d->row_bias, d->row_bias_scale);
-    RTDC_CUDA_CHECK(cudaGetLastError());
+    RTDC_CUDA_CHECK(launch_pdl(splitk_reduce_kernel, grid, dim3(256), 0, st, gp.scratch, pl.splits, pl.splits_last, pl.n_tiles, pl.m_tiles, pl.bn,
+                               d->M, d->N, n_store, d->out, d->ldo, d->bias, d->relu, gp.alpha, d->row_bias, d->row_bias_scale));
   }
   return RTDC_OK;
 }

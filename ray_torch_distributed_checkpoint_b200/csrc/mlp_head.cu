@@ -12,6 +12,7 @@
 //   dH = (dz W) * 1[H > 0] * mask_scale      -> global (the only large write)
 //   dW += dz^T H,  db += sum_rows dz          -> per-block partials, summed in block order by head_reduce
 #include "common.h"
+#include "ptx.cuh"
 #include "../../include/rtdc_b200.h"
 
 namespace rtdc {
@@ -43,6 +44,8 @@ struct HeadParams {
 template <int C>
 __global__ void __launch_bounds__(HD_THREADS, HD_BLOCKS_PER_SM)
 mlp_head_train_kernel(const HeadParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ __align__(16) float smem[];
   const int K = p.K, K4 = K >> 2, LD = K + HD_PAD;
   float* sh = smem;                        // [HD_ROWS][LD]
@@ -251,6 +254,8 @@ mlp_head_reduce_kernel(const float* __restrict__ dw_partial, const float* __rest
                        const float* __restrict__ loss_partial, int nblocks, int CK, int C, int rows, float* __restrict__ dw,
                        float* __restrict__ db, float* __restrict__ loss, const float* __restrict__ dbh_partial, int K,
                        float* __restrict__ dbh) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_part[8][32];
   {
     // elements [0, CK) are dW, elements [CK, CK + K) are the bias gradient of the layer below (when requested)
@@ -350,19 +355,18 @@ static int head_train_impl(const float* h, int ldh, const float* w, const float*
   if (part != 2) {
     if (classes == 10) {
       RTDC_CUDA_CHECK(cudaFuncSetAttribute(mlp_head_train_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-      mlp_head_train_kernel<10><<<grid, HD_THREADS, smem, st>>>(p);
+      RTDC_CUDA_CHECK(launch_pdl(mlp_head_train_kernel<10>, dim3(grid), dim3(HD_THREADS), smem, st, p));
     } else {
       RTDC_CUDA_CHECK(cudaFuncSetAttribute(mlp_head_train_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-      mlp_head_train_kernel<16><<<grid, HD_THREADS, smem, st>>>(p);
+      RTDC_CUDA_CHECK(launch_pdl(mlp_head_train_kernel<16>, dim3(grid), dim3(HD_THREADS), smem, st, p));
     }
     RTDC_CUDA_CHECK(cudaGetLastError());
   }
   if (part != 1) {
     const int CK = classes * K;
     const int total = CK + (db_below ? K : 0);
-    mlp_head_reduce_kernel<<<(total + 31) / 32, 256, 0, st>>>(p.dw_partial, p.db_partial, p.loss_partial, grid, CK, classes, rows, dw, db, loss,
-                                                            p.dbh_partial, K, db_below);
-    RTDC_CUDA_CHECK(cudaGetLastError());
+    RTDC_CUDA_CHECK(launch_pdl(mlp_head_reduce_kernel, dim3((total + 31) / 32), dim3(256), 0, st, p.dw_partial, p.db_partial, p.loss_partial, grid, CK,
+                               classes, rows, dw, db, loss, p.dbh_partial, K, db_below));
   }
   return RTDC_OK;
 }

@@ -66,6 +66,15 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may become resident while its predecessor in the
+// stream is still draining: it runs its prologue (barrier init, TMEM allocation, descriptor prefetch) on every SM the
+// predecessor has already left and blocks in pdl_wait() until the predecessor has completed and its writes are visible.
+// pdl_launch_dependents() is the predecessor's side: "my successor may be scheduled once all my blocks have got this far".
+// Both are no-ops for a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---------------------------------------------------------------- proxies / fences
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
