@@ -279,6 +279,16 @@ __device__ __forceinline__ void umma_tf32_ss_2cta(uint32_t tmem_d, uint64_t desc
       : "memory");
 }
 
+__device__ __forceinline__ void umma_f16_ss_2cta(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                                 uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 // ---------------------------------------------------------------- Philox4x32-10 (counter-based RNG)
 // Used by the fused dropout epilogue (K1/K2, reference my_ray_module.py:101,104) so a mask can be
 // replayed from (seed, step, layer, element index) alone, independent of the tiling.
