@@ -525,9 +525,12 @@ class MLPTrainEngine:
             st.wait_event(self._free[slot])                          # the step that last read this slot is done
         from_u8 = x.dtype == torch.uint8
         with torch.cuda.stream(st):
-            for t in (x, y):
-                if t.is_cuda:
-                    t.record_stream(st)                              # the caller may drop its reference right away
+            if after is None:
+                for t in (x, y):
+                    if t.is_cuda:
+                        t.record_stream(st)                          # the caller may drop its reference right away
+            # (with `after` the batch lives in a loader's ring buffer, which is reused only after the loader has seen the
+            #  consumer's stream pass this staging, see U8BatchLoader._free_ev)
             x2 = x.reshape(self.B, -1)
             self.y[slot].copy_(y, non_blocking=True)
             if from_u8:

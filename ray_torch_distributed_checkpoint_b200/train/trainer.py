@@ -256,6 +256,9 @@ class TorchTrainer:
         local_rank = int(os.environ.get("LOCAL_RANK", rank))
         if sc.num_workers != world:
             raise ValueError(f"ScalingConfig(num_workers={sc.num_workers}) but the launch has WORLD_SIZE={world}")
+        if sc.use_gpu:
+            from ..utils.affinity import bind_rank_cores
+            bind_rank_cores(local_rank, int(os.environ.get("LOCAL_WORLD_SIZE", world)))   # the native launcher pins its workers too
         created_pg = False
         if world > 1 and not dist.is_initialized():
             kwargs = {}

@@ -49,3 +49,24 @@ def bind_to_gpu_numa(device_index: int) -> Dict[str, object]:
     except Exception:
         pass
     return info
+
+
+def bind_rank_cores(local_rank: int, local_world: int) -> Dict[str, object]:
+    """Give this rank its own contiguous slice of the CPUs the process may run on (what ``rtdc-launch --bind-cores`` does for
+    workers it starts): under an external launcher (torchrun) eight unpinned ranks with their loader / checkpoint / report
+    threads migrate across all cores, and a training thread that loses its core for a moment stalls every GPU at the next
+    gradient barrier. No-op when there are fewer CPUs than ranks or ``RTDC_NO_BIND`` is set."""
+    info: Dict[str, object] = {"cpus": len(os.sched_getaffinity(0)), "bound": False}
+    if os.environ.get("RTDC_NO_BIND") or local_world <= 1:
+        return info
+    try:
+        avail = sorted(os.sched_getaffinity(0))
+        per = len(avail) // local_world
+        if per < 1:
+            return info
+        mine = avail[local_rank * per:(local_rank + 1) * per]
+        os.sched_setaffinity(0, mine)
+        info.update(cpus=len(mine), bound=True, first=mine[0])
+    except Exception:
+        pass
+    return info
