@@ -96,6 +96,33 @@ typedef struct rtdc_gemm_bf16_desc {
 } rtdc_gemm_bf16_desc;
 int rtdc_gemm_bf16(const rtdc_gemm_bf16_desc* d, void* stream);
 
+/* Softmax cross-entropy over a wide vocabulary fused with its backward (the LM head of the GPT-2 configuration): per row of the
+ * bf16 logits [rows, ld] (first `vocab` columns valid; 16-byte aligned, ld a multiple of 8) writes row_loss[row] =
+ * logsumexp(row) - row[target] (natural log, fp32) and overwrites the row IN PLACE with (softmax - onehot) * *grad_scale in
+ * bf16 — the A operand of the head's dgrad / wgrad GEMMs. Rows whose target is ignore_index (or outside [0, vocab)) get a zero
+ * loss and a zero gradient. grad_scale is a DEVICE scalar (1 / number of counted rows for a mean reduction), so a caller
+ * needs no host synchronisation to form it. One pass over HBM: a block stages its row in shared memory (rows up to 110 KB;
+ * wider ones are re-read through L2). No reference counterpart (my_ray_module.py:141 is a 10-class loss). */
+int rtdc_lm_head_ce_bf16(void* logits, long long ld, const int64_t* targets, int rows, int vocab, long long ignore_index,
+                         const float* grad_scale, float* row_loss, void* stream);
+
+/* bf16 LayerNorm over the last dimension (C a multiple of 8, <= 1024; rows 16-byte aligned), fp32 math, one warp per row.
+ * Forward: y = (x - mean) * rstd * gamma + beta (beta may be NULL); mean / rstd [rows] fp32 are saved for the backward pass.
+ * Backward: dx, and in the same pass over dy and x the weight / bias gradients (dgamma, dbeta bf16 [C]; dbeta may be NULL)
+ * through per-block partial sums in `scratch` (rtdc_layernorm_bwd_scratch_bytes; no initialisation needed) that a second
+ * small kernel adds in block order. No reference counterpart (the reference MLP has no normalisation layer). */
+int rtdc_layernorm_fwd_bf16(const void* x, long long ldx, const void* gamma, const void* beta, float eps, int rows, int C,
+                            void* y, long long ldy, float* mean, float* rstd, void* stream);
+size_t rtdc_layernorm_bwd_scratch_bytes(int rows, int C);
+int rtdc_layernorm_bwd_bf16(const void* dy, long long lddy, const void* x, long long ldx, const void* gamma, const float* mean,
+                            const float* rstd, int rows, int C, void* dx, long long lddx, void* dgamma, void* dbeta,
+                            void* scratch, size_t scratch_bytes, void* stream);
+/* out[c] = sum over rows of x[r, c] for a bf16 matrix (cols and the row pitch multiples of 8): the bias gradient of a bf16
+ * Linear layer. out is bf16 (out_fp32 == 0) or fp32; scratch: rtdc_colsum_bf16_scratch_bytes bytes, no initialisation. */
+size_t rtdc_colsum_bf16_scratch_bytes(int rows, int cols);
+int rtdc_colsum_bf16(const void* x, long long ldx, int rows, int cols, void* out, int out_fp32, void* scratch,
+                     size_t scratch_bytes, void* stream);
+
 /* out[n] = bias[n] (0 when NULL) + t * sum_k w[n*ldw + k], n < rows: the effective bias of a Linear layer whose input
  * normalisation x = s*raw + t has been folded into the GEMM (see rtdc_gemm_desc.alpha). One warp per row. */
 int rtdc_fold_input_bias(const float* w, int ldw, int rows, int cols, const float* bias, float t, float* out, void* stream);

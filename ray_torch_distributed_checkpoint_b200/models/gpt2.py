@@ -1,7 +1,8 @@
 """GPT-2 small (124 439 808 parameters with the tied LM head) for the north-star configuration
 "GPT-2 small DDP bf16 on 8xB200, synthetic 1024-token sequences, async checkpoint every N steps"
-(BASELINE.json). Not a reference capability; attention uses torch's SDPA, the gradient all-reduce,
-optimizer and checkpointing are this framework's."""
+(BASELINE.json). Not a reference capability; attention uses torch's SDPA; the gradient all-reduce, optimizer,
+checkpointing, the Linear layers (``ops.use_bf16_linears``) and the LM head + loss (``fused_head=True``:
+``ops.lm_head_cross_entropy``) are this framework's."""
 from __future__ import annotations
 
 import dataclasses
@@ -56,6 +57,7 @@ class GPT2(nn.Module):
     def __init__(self, cfg: GPT2Config = GPT2Config()):
         super().__init__()
         self.cfg = cfg
+        self.fused_head = False          # True: head GEMM + cross-entropy + its backward on this framework's kernels (ops/lm_head.py)
         self.wte = nn.Embedding(cfg.vocab_size, cfg.n_embd)
         self.wpe = nn.Embedding(cfg.n_positions, cfg.n_embd)
         self.h = nn.ModuleList(_Block(cfg) for _ in range(cfg.n_layer))
@@ -78,7 +80,11 @@ class GPT2(nn.Module):
         x = self.wte(idx) + self.wpe(pos)
         for blk in self.h:
             x = blk(x)
-        logits = F.linear(self.ln_f(x), self.wte.weight)            # tied head
+        x = self.ln_f(x)
+        if targets is not None and self.fused_head:
+            from ..ops.lm_head import lm_head_cross_entropy
+            return lm_head_cross_entropy(x, self.wte.weight, targets)
+        logits = F.linear(x, self.wte.weight)                       # tied head
         if targets is None:
             return logits
         return F.cross_entropy(logits.view(-1, logits.size(-1)).float(), targets.view(-1))

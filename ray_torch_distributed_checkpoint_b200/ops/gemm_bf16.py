@@ -93,7 +93,11 @@ class _LinearBf16Fn(torch.autograd.Function):
             dw32 = gemm_bf16(dy2, x2, a_mn=True, b_mn=True, out_dtype=torch.float32)      # dy^T x, K = tokens (split, fp32)
             dw = dw32.to(torch.bfloat16)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = dy2.sum(0, dtype=torch.float32).to(torch.bfloat16)
+            if dy2.shape[1] % 8 == 0 and dy2.data_ptr() % 16 == 0:
+                from .layernorm import colsum_bf16
+                db = colsum_bf16(dy2)                                                       # csrc/layernorm.cu, fp32 accumulation
+            else:
+                db = dy2.sum(0, dtype=torch.float32).to(torch.bfloat16)
         return dx, dw, db
 
 

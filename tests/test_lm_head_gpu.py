@@ -1,0 +1,84 @@
+"""Fused LM head (head GEMM + wide-vocabulary cross-entropy + its backward, ops/lm_head.py + csrc/lm_head.cu) against plain
+PyTorch fp32 references of the same ops."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _ce_reference(logits_bf16, targets, ignore_index=-100):
+    z = logits_bf16.float().requires_grad_(True)
+    loss = F.cross_entropy(z, targets, ignore_index=ignore_index)
+    loss.backward()
+    row = F.cross_entropy(logits_bf16.float(), targets, ignore_index=ignore_index, reduction="none")
+    return loss.detach(), z.grad, row
+
+
+@pytest.mark.parametrize("rows,vocab", [(37, 1003), (64, 50257), (5, 7), (300, 4096), (3, 60000)])
+def test_softmax_ce_kernel_matches_fp32_reference(rows, vocab):
+    """Odd vocabularies (scalar tail), one that is staged in shared memory, one too wide to be; ignored rows."""
+    from ray_torch_distributed_checkpoint_b200.ops import softmax_ce_bf16_
+    torch.manual_seed(rows + vocab)
+    ld = (vocab + 7) // 8 * 8
+    canvas = torch.full((rows, ld), 3.0, device="cuda", dtype=torch.bfloat16)
+    logits = canvas[:, :vocab]
+    logits.copy_((torch.randn(rows, vocab, device="cuda") * 3.0).to(torch.bfloat16))
+    targets = torch.randint(0, vocab, (rows,), device="cuda")
+    targets[rows // 2] = -100
+    targets[0] = vocab - 1                                             # the last column (in the scalar tail when vocab % 8)
+    ref_loss, ref_grad, ref_row = _ce_reference(logits.clone(), targets)
+    n = int((targets != -100).sum())
+    scale = torch.full((1,), 1.0 / n, device="cuda", dtype=torch.float32)
+    row_loss = softmax_ce_bf16_(logits, targets, scale)
+    assert (row_loss - ref_row).abs().max().item() < 2e-4 * max(1.0, ref_row.abs().max().item())
+    assert abs(row_loss.sum().item() / n - ref_loss.item()) < 1e-4 * max(1.0, abs(ref_loss.item()))
+    # the gradient replaced the logits; bf16 rounding of values <= 1/n
+    assert (logits.float() - ref_grad).abs().max().item() < 4e-3 / n + 1e-7
+    assert (logits[rows // 2] == 0).all() and row_loss[rows // 2].item() == 0.0
+    if ld > vocab:
+        assert (canvas[:, vocab:] == 3).all()                          # padding columns untouched
+
+
+def test_lm_head_cross_entropy_loss_and_gradients():
+    """Forward value, d/dh and d/dW (tied-head shape: W [V, C], odd V) against fp32 autograd over the same bf16 inputs."""
+    from ray_torch_distributed_checkpoint_b200.ops import lm_head_cross_entropy
+    torch.manual_seed(3)
+    T, Cin, V = 640, 256, 5003
+    h = (torch.randn(2, T // 2, Cin, device="cuda") * 0.5).to(torch.bfloat16).requires_grad_(True)
+    w = (torch.randn(V, Cin, device="cuda") * 0.05).to(torch.bfloat16).requires_grad_(True)
+    tgt = torch.randint(0, V, (2, T // 2), device="cuda")
+    tgt[0, :7] = -100
+    loss = lm_head_cross_entropy(h, w, tgt)
+    (loss * 2.0).backward()                                            # an upstream factor reaches both gradients
+
+    h32 = h.detach().float().requires_grad_(True)
+    w32 = w.detach().float().requires_grad_(True)
+    ref = F.cross_entropy((h32.view(-1, Cin) @ w32.t()), tgt.view(-1))
+    (ref * 2.0).backward()
+    assert abs(loss.item() - ref.item()) < 3e-3 * abs(ref.item())
+    assert h.grad.shape == h.shape and w.grad.shape == w.shape and h.grad.dtype == torch.bfloat16
+    for got, want in ((h.grad, h32.grad), (w.grad, w32.grad)):
+        err = (got.float() - want).abs().max().item()
+        assert err < 2e-2 * want.abs().max().item() + 1e-6, (err, want.abs().max().item())
+
+
+def test_gpt2_fused_head_matches_plain_head():
+    """The GPT-2 model with ``fused_head`` gives the same loss and the same tied-embedding gradient as the stock head."""
+    from ray_torch_distributed_checkpoint_b200.models import GPT2, GPT2Config
+    torch.manual_seed(5)
+    cfg = GPT2Config(vocab_size=1001, n_positions=64, n_embd=64, n_layer=2, n_head=4)
+    a = GPT2(cfg).cuda().to(torch.bfloat16)
+    b = GPT2(cfg).cuda().to(torch.bfloat16)
+    b.load_state_dict(a.state_dict())
+    b.fused_head = True
+    idx = torch.randint(0, 1001, (4, 64), device="cuda")
+    tgt = torch.randint(0, 1001, (4, 64), device="cuda")
+    la, lb = a(idx, tgt), b(idx, tgt)
+    la.backward()
+    lb.backward()
+    assert abs(la.item() - lb.item()) < 5e-3 * abs(la.item())
+    ga, gb = a.wte.weight.grad.float(), b.wte.weight.grad.float()
+    assert (ga - gb).abs().max().item() < 3e-2 * ga.abs().max().item() + 1e-6
+    g1, g2 = a.h[0].c_fc.weight.grad.float(), b.h[0].c_fc.weight.grad.float()
+    assert (g1 - g2).abs().max().item() < 8e-2 * g1.abs().max().item() + 1e-6

@@ -28,9 +28,14 @@ def main():
     ap.add_argument("--ckpt-every", type=int, default=0, help="async checkpoint every N steps (ours) / torch.save (torch)")
     ap.add_argument("--linear", choices=["ours", "torch"], default=None, help="gpt2: nn.Linear on the repo's bf16 tcgen05 GEMM (default with --ddp ours) or cuBLAS")
     ap.add_argument("--opt", choices=["ours", "torch"], default=None, help="gpt2: the repo's fused bf16 AdamW kernel over the flat arena (default with --ddp ours) or torch's fused AdamW")
+    ap.add_argument("--head", choices=["ours", "torch"], default=None, help="gpt2: LM head GEMM + cross-entropy + backward on the repo's kernels (ops.lm_head_cross_entropy; default with --linear ours) or F.linear + F.cross_entropy")
+    ap.add_argument("--norm", choices=["ours", "torch"], default=None, help="gpt2: LayerNorm forward / backward on the repo's kernels (ops.use_fused_layernorm; default with --linear ours) or torch's")
+    ap.add_argument("--vocab", type=int, default=50257, help="gpt2: vocabulary size (50304 = padded to a multiple of 64, the usual work-around for cuBLAS's unaligned-N fallback)")
     args = ap.parse_args()
     args.linear = args.linear or ("ours" if args.ddp == "ours" else "torch")
     args.opt = args.opt or ("ours" if args.ddp == "ours" else "torch")
+    args.head = args.head or args.linear
+    args.norm = args.norm or args.linear
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -48,12 +53,16 @@ def main():
         per_sample = 1
     else:
         B = args.batch or 16
-        model = GPT2(GPT2Config()).to(dev, dtype=torch.bfloat16)
+        model = GPT2(GPT2Config(vocab_size=args.vocab)).to(dev, dtype=torch.bfloat16)
         if args.linear == "ours":
             from ray_torch_distributed_checkpoint_b200.ops import use_bf16_linears
             use_bf16_linears(model)                      # 48 Linear layers: forward, dgrad, wgrad on csrc/gemm_bf16.cu
-        idx = torch.randint(0, 50257, (B, 1024), device=dev)
-        tgt = torch.randint(0, 50257, (B, 1024), device=dev)
+        model.fused_head = args.head == "ours"           # tied head + loss: gemm_bf16 + csrc/lm_head.cu, no fp32 logits
+        if args.norm == "ours":
+            from ray_torch_distributed_checkpoint_b200.ops import use_fused_layernorm
+            use_fused_layernorm(model)                   # 25 LayerNorms: csrc/layernorm.cu
+        idx = torch.randint(0, args.vocab, (B, 1024), device=dev)
+        tgt = torch.randint(0, args.vocab, (B, 1024), device=dev)
         loss_of = lambda m: m(idx, tgt)
         if args.opt == "ours":
             from ray_torch_distributed_checkpoint_b200.optim import AdamW
@@ -118,7 +127,8 @@ def main():
                           "ms_per_step": round(ms / args.steps, 3), "samples_per_s": round(B * world * args.steps / (ms / 1e3), 1),
                           "tokens_per_s": round(B * world * per_sample * args.steps / (ms / 1e3), 1) if per_sample > 1 else None,
                           "ms_per_step_until_durable": round((ms + durable_extra_ms) / args.steps, 3),
-                          "linear": args.linear if args.model == "gpt2" else "torch", "optimizer": args.opt if args.model == "gpt2" else "torch",
+                          "linear": args.linear if args.model == "gpt2" else "torch", "head": args.head if args.model == "gpt2" else "torch", "norm": args.norm if args.model == "gpt2" else "torch",
+                          "vocab": args.vocab if args.model == "gpt2" else None, "optimizer": args.opt if args.model == "gpt2" else "torch",
                           "ckpt_every": args.ckpt_every, "loss": round(float(loss), 4), "dtype": "bf16"}), flush=True)
     if world > 1:
         dist.barrier()
