@@ -15,7 +15,7 @@
 namespace rtdc {
 
 constexpr int LN_FWD_THREADS = 256;
-constexpr int LN_BWD_THREADS = 384;          // 12 warps, one block per SM: up to 170 registers per thread
+constexpr int LN_BWD_THREADS = 256;          // 8 warps, one block per SM (the row in flight + the prefetched one + 48 column sums per lane)
 constexpr int LN_MAX_NVL = 4;                // vectors of 8 per lane: C <= 1024
 
 __device__ __forceinline__ void ln_unpack8(const uint4& q, float* x) {
@@ -63,15 +63,30 @@ ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, const __nv_bfl
   }
   const float inv_c = 1.f / static_cast<float>(C);
   const int wpb = LN_FWD_THREADS / 32;
-  for (int row = blockIdx.x * wpb + warp; row < rows; row += gridDim.x * wpb) {
+  // software pipeline: the next row's loads are issued before this row's arithmetic, so a warp always has a row in flight
+  const int stride = gridDim.x * wpb;
+  int row = blockIdx.x * wpb + warp;
+  uint4 q[NVL];
+  if (row < rows) {
     const uint4* xr = reinterpret_cast<const uint4*>(x + static_cast<long long>(row) * ldx);
+#pragma unroll
+    for (int k = 0; k < NVL; ++k)
+      if (lane + 32 * k < nvec) q[k] = xr[lane + 32 * k];
+  }
+  for (; row < rows; row += stride) {
+    uint4 qn[NVL];
+    if (row + stride < rows) {
+      const uint4* xn = reinterpret_cast<const uint4*>(x + static_cast<long long>(row + stride) * ldx);
+#pragma unroll
+      for (int k = 0; k < NVL; ++k)
+        if (lane + 32 * k < nvec) qn[k] = xn[lane + 32 * k];
+    }
     float xv[NVL][8];
     float s = 0.f;
 #pragma unroll
     for (int k = 0; k < NVL; ++k) {
-      const int v = lane + 32 * k;
-      if (v < nvec) {
-        ln_unpack8(xr[v], xv[k]);
+      if (lane + 32 * k < nvec) {
+        ln_unpack8(q[k], xv[k]);
 #pragma unroll
         for (int j = 0; j < 8; ++j) s += xv[k][j];
       }
@@ -104,6 +119,8 @@ ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, const __nv_bfl
       mean_out[row] = mean;
       rstd_out[row] = rstd;
     }
+#pragma unroll
+    for (int k = 0; k < NVL; ++k) q[k] = qn[k];
   }
 }
 
@@ -128,16 +145,36 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long long lddy, const __nv_b
   }
   for (int i = threadIdx.x; i < 2 * C; i += LN_BWD_THREADS) ln_acc[i] = 0.f;
   const float inv_c = 1.f / static_cast<float>(C);
-  for (int row = blockIdx.x * WPB + warp; row < rows; row += gridDim.x * WPB) {
+  // software pipeline: the next row's loads are issued before this row's arithmetic
+  const int stride = gridDim.x * WPB;
+  int row = blockIdx.x * WPB + warp;
+  uint4 qx[NVL], qd[NVL];
+  float mu = 0.f, rs = 0.f;
+  if (row < rows) {
+    mu = mean[row];
+    rs = rstd[row];
     const uint4* xr = reinterpret_cast<const uint4*>(x + static_cast<long long>(row) * ldx);
     const uint4* dyr = reinterpret_cast<const uint4*>(dy + static_cast<long long>(row) * lddy);
-    uint4 qx[NVL], qd[NVL];
 #pragma unroll
-    for (int k = 0; k < NVL; ++k) {                        // all loads of the row in flight before the first use
+    for (int k = 0; k < NVL; ++k) {
       const int v = lane + 32 * k;
       if (v < nvec) { qx[k] = xr[v]; qd[k] = dyr[v]; }
     }
-    const float mu = mean[row], rs = rstd[row];
+  }
+  for (; row < rows; row += stride) {
+    uint4 nx[NVL], nd[NVL];
+    float nmu = 0.f, nrs = 0.f;
+    if (row + stride < rows) {
+      nmu = mean[row + stride];
+      nrs = rstd[row + stride];
+      const uint4* xn = reinterpret_cast<const uint4*>(x + static_cast<long long>(row + stride) * ldx);
+      const uint4* dyn = reinterpret_cast<const uint4*>(dy + static_cast<long long>(row + stride) * lddy);
+#pragma unroll
+      for (int k = 0; k < NVL; ++k) {
+        const int v = lane + 32 * k;
+        if (v < nvec) { nx[k] = xn[v]; nd[k] = dyn[v]; }
+      }
+    }
     float xh[NVL][8], gv[NVL][8];
     float c1 = 0.f, c2 = 0.f;
 #pragma unroll
@@ -170,6 +207,10 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long long lddy, const __nv_b
         dxr[v] = ln_pack8(o);
       }
     }
+#pragma unroll
+    for (int k = 0; k < NVL; ++k) { qx[k] = nx[k]; qd[k] = nd[k]; }
+    mu = nmu;
+    rs = nrs;
   }
   // the block's warps add their column sums in warp order
   __syncthreads();

@@ -115,6 +115,7 @@ class SGD(_FlatOptimizer):
         self.m_arena = torch.zeros_like(self.p_arena) if momentum != 0 else None
         self._steps = 0
         self.state_dev = ops.SgdState(self.device, lr, momentum, dampening, weight_decay, nesterov) if self.use_kernels else None
+        self._lr_dev = lr
         self.param_groups = [dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay, nesterov=nesterov,
                                   maximize=False, foreach=None, differentiable=False, fused=None,
                                   params=list(range(len(self.params))))]
@@ -124,8 +125,9 @@ class SGD(_FlatOptimizer):
         self._gather_grads()
         g = self.param_groups[0]
         if self.use_kernels:
-            if g["lr"] != self.state_dev.host.lr:       # LR schedulers write param_groups[0]['lr']
-                self.state_dev.update(lr=g["lr"])
+            if g["lr"] != self._lr_dev:                 # LR schedulers write param_groups[0]['lr'] (compare the value as
+                self.state_dev.update(lr=g["lr"])       # given: the device mirror holds it rounded to fp32)
+                self._lr_dev = g["lr"]
             ops.sgd_step(self.p_arena, self.g_arena, self.m_arena, self.state_dev)
             if self._steps == 0:
                 ops.counter_advance(None, self.state_dev)
@@ -164,6 +166,7 @@ class SGD(_FlatOptimizer):
             self.state_dev.update(lr=g["lr"], momentum=g["momentum"], dampening=g["dampening"],
                                   weight_decay=g["weight_decay"], nesterov=int(g["nesterov"]),
                                   first_step=0 if sd["state"] else 1)
+            self._lr_dev = g["lr"]
 
 
 class Adam(_FlatOptimizer):
@@ -181,6 +184,7 @@ class Adam(_FlatOptimizer):
         self.v_arena = torch.zeros_like(self.m_arena)
         self._steps = 0
         self.state_dev = ops.AdamState(self.device, lr, betas, eps, weight_decay, decoupled_weight_decay) if self.use_kernels else None
+        self._lr_dev = lr
         self.param_groups = [dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay, amsgrad=False, maximize=False,
                                   foreach=None, capturable=False, differentiable=False, fused=None,
                                   decoupled_weight_decay=decoupled_weight_decay, params=list(range(len(self.params))))]
@@ -191,8 +195,9 @@ class Adam(_FlatOptimizer):
         g = self.param_groups[0]
         self._steps += 1
         if self.use_kernels:
-            if g["lr"] != self.state_dev.host.lr:
-                self.state_dev.update(lr=g["lr"])
+            if g["lr"] != self._lr_dev:                 # as given, not the fp32-rounded device mirror (that compare never
+                self.state_dev.update(lr=g["lr"])       # matched: one device round trip per step)
+                self._lr_dev = g["lr"]
             ops.adam_step(self.p_arena, self.g_arena, self.m_arena, self.v_arena, self.state_dev,
                           master=self.master if self.bf16 else None)
             return
@@ -228,6 +233,7 @@ class Adam(_FlatOptimizer):
         if self.use_kernels:
             self.state_dev.update(lr=g["lr"], beta1=g["betas"][0], beta2=g["betas"][1], eps=g["eps"],
                                   weight_decay=g["weight_decay"], step=self._steps)
+            self._lr_dev = g["lr"]
 
 
 class AdamW(Adam):

@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--linear", choices=["ours", "torch"], default=None, help="gpt2: nn.Linear on the repo's bf16 tcgen05 GEMM (default with --ddp ours) or cuBLAS")
     ap.add_argument("--opt", choices=["ours", "torch"], default=None, help="gpt2: the repo's fused bf16 AdamW kernel over the flat arena (default with --ddp ours) or torch's fused AdamW")
     ap.add_argument("--head", choices=["ours", "torch"], default=None, help="gpt2: LM head GEMM + cross-entropy + backward on the repo's kernels (ops.lm_head_cross_entropy; default with --linear ours) or F.linear + F.cross_entropy")
+    ap.add_argument("--graph", action="store_true", help="capture the whole step (zero_grad, forward, backward, optimizer) in one CUDA graph (utils.GraphedStep); one GPU, no checkpoints")
     ap.add_argument("--norm", choices=["ours", "torch"], default=None, help="gpt2: LayerNorm forward / backward on the repo's kernels (ops.use_fused_layernorm; default with --linear ours) or torch's")
     ap.add_argument("--vocab", type=int, default=50257, help="gpt2: vocabulary size (50304 = padded to a multiple of 64, the usual work-around for cuBLAS's unaligned-N fallback)")
     args = ap.parse_args()
@@ -68,7 +69,7 @@ def main():
             from ray_torch_distributed_checkpoint_b200.optim import AdamW
             opt_cls = lambda m: AdamW(m, lr=3e-4)        # adam_bf16_kernel: fp32 master + moments, one launch over the arena
         else:
-            opt_cls = lambda m: torch.optim.AdamW(m.parameters(), lr=3e-4, fused=True)
+            opt_cls = lambda m: torch.optim.AdamW(m.parameters(), lr=3e-4, fused=True, capturable=args.graph)
         per_sample = 1024
     if world > 1:
         if args.ddp == "ours":
@@ -99,6 +100,13 @@ def main():
                 torch.save(state, os.path.join(ckpt_dir, "latest_model.pt"))
         return loss
 
+    if args.graph:
+        if world > 1 or args.ckpt_every:
+            raise SystemExit("--graph is for one GPU without checkpoints")
+        from ray_torch_distributed_checkpoint_b200.utils import GraphedStep
+        eager_step = step
+        graphed = GraphedStep(lambda: eager_step(0), warmup=3)
+        step = lambda i: graphed()
     for i in range(args.warmup):
         step(i)
     if world > 1:
@@ -129,7 +137,7 @@ def main():
                           "ms_per_step_until_durable": round((ms + durable_extra_ms) / args.steps, 3),
                           "linear": args.linear if args.model == "gpt2" else "torch", "head": args.head if args.model == "gpt2" else "torch", "norm": args.norm if args.model == "gpt2" else "torch",
                           "vocab": args.vocab if args.model == "gpt2" else None, "optimizer": args.opt if args.model == "gpt2" else "torch",
-                          "ckpt_every": args.ckpt_every, "loss": round(float(loss), 4), "dtype": "bf16"}), flush=True)
+                          "ckpt_every": args.ckpt_every, "cuda_graph": bool(args.graph), "loss": round(float(loss), 4), "dtype": "bf16"}), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
