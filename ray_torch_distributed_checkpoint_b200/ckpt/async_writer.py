@@ -35,16 +35,34 @@ def _align(n: int) -> int:
     return (n + _ALIGN - 1) // _ALIGN * _ALIGN
 
 
-def atomic_torch_save(obj: Any, path: str) -> None:
+FAST_WRITER_MIN_BYTES = 64 << 20     # states at least this big go through the parallel writer (ckpt/fast_zip.py)
+
+
+def atomic_torch_save(obj: Any, path: str, parallel: Optional[bool] = None) -> None:
     """``torch.save`` to a temp file in the same directory, then ``rename`` (readers never see a
-    partial file; concurrent writers of the same name cannot interleave)."""
+    partial file; concurrent writers of the same name cannot interleave). States of 64 MB and more are written by the
+    parallel archive writer (same entries and contents, ``torch.load``-able; ``parallel=False`` or
+    ``RTDC_CKPT_WRITER=torch`` keeps stock ``torch.save``), which falls back to ``torch.save`` if it cannot handle the object."""
     d = os.path.dirname(os.path.abspath(path)) or "."
     os.makedirs(d, exist_ok=True)
     fd, tmp = tempfile.mkstemp(prefix="." + os.path.basename(path) + ".", suffix=".tmp", dir=d)
     os.close(fd)
     try:
-        # the archive's root folder is the file stem, as for a direct torch.save(obj, path)
-        _save_with_stem(obj, tmp, os.path.basename(path))
+        done = False
+        if parallel is None:
+            from .fast_zip import state_bytes
+            parallel = os.environ.get("RTDC_CKPT_WRITER", "") != "torch" and state_bytes(obj) >= FAST_WRITER_MIN_BYTES
+        if parallel:
+            try:
+                from . import fast_zip
+                fast_zip.save(obj, tmp, archive_name=os.path.splitext(os.path.basename(path))[0])
+                done = True
+            except Exception as e:                       # private PyTorch hook moved, exotic object, ...: the stock path always works
+                import warnings
+                warnings.warn(f"parallel checkpoint writer unavailable ({type(e).__name__}: {e}); using torch.save")
+        if not done:
+            # the archive's root folder is the file stem, as for a direct torch.save(obj, path)
+            _save_with_stem(obj, tmp, os.path.basename(path))
         os.replace(tmp, path)
     except BaseException:
         if os.path.exists(tmp):
@@ -241,15 +259,20 @@ class AsyncCheckpointer:
                 if n:
                     slot.host[off:off + n].view(t.dtype).copy_(t.detach().reshape(-1))
 
-        def cpu_state():
+        def cpu_state(alias: bool = False):
+            """The state as CPU tensors, each owning a storage of exactly its own size (as in a stock state_dict). By default
+            they are clones; ``alias=True`` gives zero-copy views of the pinned snapshot buffer, valid until the slot is
+            reused (what ``save`` hands to the writer: no staging copy of a gigabyte-sized state)."""
             if done_event is not None:
                 done_event.synchronize()
             mapping = {}
+            host_np = slot.host.numpy() if alias else None
             for k, t in uniq.items():
                 off, n = offsets[k]
-                # clone out of the pinned ring so the saved file does not alias a reusable buffer and
-                # each tensor owns a storage of exactly its own size (as in a stock state_dict)
-                mapping[k] = slot.host[off:off + n].view(t.dtype).reshape(t.shape).clone()
+                if alias and n:
+                    mapping[k] = torch.frombuffer(host_np, dtype=t.dtype, count=t.numel(), offset=off).reshape(t.shape)
+                else:
+                    mapping[k] = slot.host[off:off + n].view(t.dtype).reshape(t.shape).clone()
             return self._rebuild(state, mapping)
 
         self.stats["snapshots"] += 1
@@ -266,11 +289,15 @@ class AsyncCheckpointer:
             filenames = [filenames]
         os.makedirs(directory, exist_ok=True)
         cpu_state, slot = self.snapshot(state)
+        from .fast_zip import state_bytes
+        big = state_bytes(state) >= FAST_WRITER_MIN_BYTES
 
         def job():
             import time
             t0 = time.time()
-            obj = cpu_state()
+            # big states are handed to the writer as views of the pinned snapshot buffer (no staging copy of a gigabyte);
+            # obj is dropped before this job ends and the slot stays busy until then. Small ones keep the cloning path.
+            obj = cpu_state(alias=big)
             t1 = time.time()
             first = os.path.join(directory, filenames[0])
             atomic_torch_save(obj, first)

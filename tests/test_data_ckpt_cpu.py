@@ -161,3 +161,72 @@ def test_philox_reference_statistics_and_determinism():
     assert abs(m.mean() - 0.75) < 0.01
     assert np.array_equal(m, dropout_keep_mask(64, 512, 0.25, seed=7, step=1, salt=2))
     assert not np.array_equal(m, dropout_keep_mask(64, 512, 0.25, seed=7, step=2, salt=2))
+
+
+def test_parallel_archive_writer_matches_stock_torch_save(tmp_path):
+    """ckpt/fast_zip.py: same entries, order and contents as torch.save of the same object; valid CRCs; 64-byte aligned
+    payloads; loadable with weights_only=True (also through mmap and with zip64 fields forced)."""
+    import struct
+    from ray_torch_distributed_checkpoint_b200.ckpt import fast_zip
+    state = _ref_state()
+    state["extra"] = {"empty": torch.empty(0), "half": torch.randn(33, 7).to(torch.bfloat16), "ints": torch.arange(10)}
+    ours, ref = tmp_path / "a" / "latest_model.pt", tmp_path / "b" / "latest_model.pt"
+    os.makedirs(ours.parent), os.makedirs(ref.parent)
+    n = fast_zip.save(state, str(ours), threads=3, chunk_bytes=1 << 16)
+    torch.save(state, str(ref))
+    assert n == os.path.getsize(ours)
+    za, zb = zipfile.ZipFile(ours), zipfile.ZipFile(ref)
+    assert za.testzip() is None
+    assert [i.filename for i in za.infolist()] == [i.filename for i in zb.infolist()]
+    for i in za.infolist():
+        if not i.filename.endswith("serialization_id"):
+            assert za.read(i.filename) == zb.read(i.filename), i.filename
+    raw = ours.read_bytes()
+    for i in za.infolist():
+        fnl, exl = struct.unpack("<HH", raw[i.header_offset + 26:i.header_offset + 30])
+        assert (i.header_offset + 30 + fnl + exl) % 64 == 0, i.filename
+    for kw in ({}, {"mmap": True}):
+        got = torch.load(str(ours), weights_only=True, **kw)
+        assert torch.equal(got["model_state_dict"]["linear_relu_stack.0.weight"], state["model_state_dict"]["linear_relu_stack.0.weight"])
+        assert torch.equal(got["extra"]["half"], state["extra"]["half"]) and got["extra"]["empty"].numel() == 0
+        assert got["optimizer_state_dict"]["param_groups"][0]["momentum"] == 0.9
+    z64 = tmp_path / "z64.pt"
+    fast_zip.save(state, str(z64), force_zip64=True)
+    assert zipfile.ZipFile(z64).testzip() is None
+    assert torch.equal(torch.load(str(z64), weights_only=True)["extra"]["ints"], state["extra"]["ints"])
+
+
+def test_big_states_take_the_parallel_writer_and_small_ones_torch_save(tmp_path, monkeypatch):
+    from ray_torch_distributed_checkpoint_b200.ckpt import async_writer, fast_zip
+    calls = []
+    real = fast_zip.save
+    monkeypatch.setattr(fast_zip, "save", lambda *a, **k: (calls.append(a[1]), real(*a, **k))[1])
+    state = _ref_state()
+    ckpt.atomic_torch_save(state, str(tmp_path / "small" / "latest_model.pt"))
+    assert not calls                                                        # 5 MB: stock torch.save
+    monkeypatch.setattr(async_writer, "FAST_WRITER_MIN_BYTES", 1 << 20)
+    cp = ckpt.AsyncCheckpointer("cpu")
+    pending = cp.save(state, str(tmp_path / "big"), ["latest_model.pt", "best_model.pt"])
+    w = state["model_state_dict"]["linear_relu_stack.0.weight"]
+    expect = w.clone()
+    w.add_(1.0)                                                             # the snapshot is isolated from later updates
+    pending.result()
+    assert len(calls) == 2 and all(".latest_model.pt." in c or ".best_model.pt." in c for c in calls)
+    for name in ("latest_model.pt", "best_model.pt"):
+        got = torch.load(str(tmp_path / "big" / name), weights_only=True)
+        assert torch.equal(got["model_state_dict"]["linear_relu_stack.0.weight"], expect)
+        assert zipfile.ZipFile(tmp_path / "big" / name).namelist()[0] == name[:-3] + "/data.pkl"
+    monkeypatch.setenv("RTDC_CKPT_WRITER", "torch")
+    calls.clear()
+    ckpt.atomic_torch_save(state, str(tmp_path / "forced" / "latest_model.pt"))
+    assert not calls
+    cp.close()
+
+
+def test_parallel_writer_failure_falls_back_to_torch_save(tmp_path, monkeypatch):
+    from ray_torch_distributed_checkpoint_b200.ckpt import fast_zip
+    monkeypatch.setattr(fast_zip, "save", lambda *a, **k: (_ for _ in ()).throw(RuntimeError("moved")))
+    state = _ref_state()
+    with pytest.warns(UserWarning, match="parallel checkpoint writer unavailable"):
+        ckpt.atomic_torch_save(state, str(tmp_path / "latest_model.pt"), parallel=True)
+    assert torch.load(str(tmp_path / "latest_model.pt"), weights_only=True)["epoch"] == 0
