@@ -731,13 +731,30 @@ class CronSchedule:
             return d_ok and w_ok
         return d_ok or w_ok
 
+    def _day_matches(self, d) -> bool:
+        _, _, dom, mo, dow = self.fields
+        if d.month not in mo:
+            return False
+        d_ok, w_ok = d.day in dom, (d.isoweekday() % 7) in dow
+        return (d_ok and w_ok) if (self.dom_star or self.dow_star) else (d_ok or w_ok)
+
     def next_after(self, t):
+        """First matching minute strictly after ``t``. Walks days, not minutes (``0 0 29 2 *`` is up to eight years away:
+        1896 -> 1904 skips the non-leap year 1900)."""
         import datetime as dt
         t = t.replace(second=0, microsecond=0) + dt.timedelta(minutes=1)
-        for _ in range(366 * 24 * 60):
-            if self.matches(t):
-                return t
-            t += dt.timedelta(minutes=1)
+        minutes, hours = sorted(self.fields[0]), sorted(self.fields[1])
+        day = t.replace(hour=0, minute=0)
+        for i in range(366 * 8 + 2):
+            if self._day_matches(day):
+                for h in hours:
+                    if i == 0 and h < t.hour:
+                        continue
+                    for m in minutes:
+                        if i == 0 and h == t.hour and m < t.minute:
+                            continue
+                        return day.replace(hour=h, minute=m)
+            day += dt.timedelta(days=1)
         raise ValueError(f"cron expression {self.expr!r} never fires")
 
 
