@@ -231,7 +231,13 @@ def run_ours(args):
     #    the device-timed `value`: a step's interval holds the step's kernels, not the PCIe link;
     #  * "stream" (dataset in pinned host memory, every step's pixels + labels cross PCIe by DMA) gives the contract `e2e`.
     runs = {}
-    for transfer in (["resident", "stream"] if args.input_transfer == "both" else [args.input_transfer]):
+    # the resident transfer holds the whole synthetic dataset (B x world x steps-per-epoch rows) in every GPU's HBM: lift the
+    # loader's conservative 4 GiB default for long --steps, and stream when even 64 GiB would not do
+    os.environ.setdefault("RTDC_RESIDENT_MAX_BYTES", str(64 << 30))
+    transfers = ["resident", "stream"] if args.input_transfer == "both" else [args.input_transfer]
+    if B * world * S * 785 > int(os.environ["RTDC_RESIDENT_MAX_BYTES"]):
+        transfers = [t for t in transfers if t != "resident"] or ["stream"]
+    for transfer in transfers:
         per_rank, clocks, wall, result = _fit_once(my_module, args, transfer, world, rank, local, B, S, epochs, home, transfer)
         if rank == 0:
             dev_blocks, e2e_blocks, host_ms = _blocks(per_rank, warm_epochs, R, S)
@@ -240,10 +246,9 @@ def run_ours(args):
                                   extra=per_rank[0].get("extra", {}),
                                   metrics={k: v for k, v in (getattr(result, "metrics", None) or {}).items() if not str(k).startswith("_")})
     if rank == 0:
-        v_run = runs.get("resident") or runs[args.input_transfer]
-        e_run = runs.get("stream") or runs[args.input_transfer]
-        v_name = "resident" if "resident" in runs else args.input_transfer
-        e_name = "stream" if "stream" in runs else args.input_transfer
+        v_name = "resident" if "resident" in runs else next(iter(runs))
+        e_name = "stream" if "stream" in runs else next(iter(runs))
+        v_run, e_run = runs[v_name], runs[e_name]
         ms, ms_min, ms_max = v_run["dev"]
         extra = v_run["extra"]
         lps = int(extra.get("launches_per_train_step", 0))

@@ -128,7 +128,8 @@ def prepare_data_loader(data_loader, *, add_dist_sampler: bool = True, move_to_d
     kept as bytes, batches are ``data.U8Images`` that normalise themselves on the GPU (or are consumed raw by the
     engine-backed model of :func:`prepare_model`). ``transfer`` (default: ``$RTDC_INPUT_TRANSFER`` or ``"auto"``) picks how a
     shuffled batch reaches the device, see ``data.U8BatchLoader``: ``"resident"`` (dataset uploaded once, exact
-    ``DistributedSampler`` shuffle by a gather kernel; what ``"auto"`` picks when the dataset fits), ``"stream"`` (dataset
+    ``DistributedSampler`` shuffle by a gather kernel; what ``"auto"`` picks when the dataset fits ``$RTDC_RESIDENT_MAX_BYTES``,
+    4 GiB by default), ``"stream"`` (dataset
     in pinned host memory, every step's pixels cross PCIe by DMA, two-level block shuffle) or ``"host_gather"`` (exact
     shuffle gathered by host threads).
     """
@@ -146,7 +147,8 @@ def prepare_data_loader(data_loader, *, add_dist_sampler: bool = True, move_to_d
             return U8BatchLoader(imgs, labels, data_loader.batch_size, device, shuffle=isinstance(data_loader.sampler, tud.RandomSampler),
                                  world=world if shard else 1, rank=rank if shard else 0, drop_last=data_loader.drop_last,
                                  mean=mean, std=std, wrap=True, timed=timed, lookahead=3,
-                                 transfer=transfer or os.environ.get("RTDC_INPUT_TRANSFER", "auto"))
+                                 transfer=transfer or os.environ.get("RTDC_INPUT_TRANSFER", "auto"),
+                                 resident_max_bytes=int(os.environ.get("RTDC_RESIDENT_MAX_BYTES", 4 << 30)))
     if add_dist_sampler and world > 1:
         data_loader = shard_data_loader(data_loader, world, rank)
     if move_to_device:
