@@ -211,3 +211,20 @@ def test_heartbeat_timeout_fails_a_silent_worker(tmp_path):
     with pytest.raises(TrainingFailedError, match="no worker activity"):
         trainer.fit()
     assert RunConfig().worker_report_timeout_s == 600.0               # finite by default
+
+
+def test_fit_in_spmd_mode_under_torchrun_on_gloo(tmp_path):
+    """fit() inside ranks that torch.distributed.run started (how bench.py runs at N > 1): reports with checkpoints on the
+    report thread's own gloo group, retention, and the Result on every rank."""
+    import socket
+    import subprocess
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    worker = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_spmd_cpu_worker.py")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), worker, str(tmp_path / "store")]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-4000:]
+    assert "SPMD_OK rank 0" in out.stdout and "SPMD_OK rank 1" in out.stdout
